@@ -1,0 +1,131 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes loaders for the CPU checkers of the compute pass.
+
+Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` /
+``--impl reference`` legs may import this package.  The product package
+(``raytracing_engine_b200``) never does; it fails loudly without its CUDA library.
+
+Three checkers share one calling convention (see ``oracle/ref_driver.cpp``):
+
+* ``ref``   oracle/_ref/librtce_ref.so      the reference's own compute.glsl +
+            utilities.glsl compiled as C++ (<= 8 spheres, <= 9 levels, RENDER_DIST 1000)
+* ``refx``  oracle/_ref/librtce_ref_ext.so  same text, MAX_OBJECTS / imgs[] raised
+* ``port``  oracle/librtce_oracle.so        plain-C restatement (any size)
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIBS = {
+    "ref": (os.path.join(_HERE, "_ref", "librtce_ref.so"), "rtce_ref"),
+    "refx": (os.path.join(_HERE, "_ref", "librtce_ref_ext.so"), "rtce_refx"),
+    "port": (os.path.join(_HERE, "librtce_oracle.so"), "rtce_oracle"),
+}
+_loaded: dict = {}
+
+
+def build(verbose: bool = False) -> None:
+    """Compile the C port, and oracle/_ref when /root/reference is present."""
+    out = subprocess.run(["make", "-C", _HERE, "all"], capture_output=True, text=True)
+    if verbose or out.returncode != 0:
+        print(out.stdout[-4000:], out.stderr[-4000:])
+    if out.returncode != 0:
+        raise RuntimeError("oracle build failed")
+
+
+def available(kind: str) -> bool:
+    return os.path.exists(_LIBS[kind][0])
+
+
+class Oracle:
+    def __init__(self, kind: str):
+        path, prefix = _LIBS[kind]
+        if not os.path.exists(path):
+            raise FileNotFoundError(f"oracle '{kind}' not built: {path} (run `make -C oracle`)")
+        self.kind = kind
+        self.lib = C.CDLL(path)
+        g = lambda n: getattr(self.lib, f"{prefix}_{n}")
+        self._trace = g("trace")
+        self._trace.restype = C.c_int
+        self._trace.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                C.c_float, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        self._level_count = g("level_count"); self._level_count.restype = C.c_int
+        self._level_count.argtypes = [C.c_float, C.c_int]
+        self._level_dims = g("level_dims"); self._level_dims.restype = None
+        self._level_dims.argtypes = [C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p, C.c_void_p]
+        self._image_size = g("image_size"); self._image_size.restype = None
+        self._image_size.argtypes = [C.c_int, C.c_int, C.c_float, C.c_float, C.c_void_p]
+        g("max_objects").restype = C.c_int
+        g("max_levels").restype = C.c_int
+        g("render_dist").restype = C.c_float
+        self.max_objects = g("max_objects")()
+        self.max_levels = g("max_levels")()
+        self.fixed_render_dist = g("render_dist")()
+
+    def level_count(self, view_w: float, resize_rule: bool = False) -> int:
+        return int(self._level_count(view_w, int(resize_rule)))
+
+    def level_dims(self, levels: int, view_w: float, view_h: float):
+        out = []
+        w, h = C.c_int(), C.c_int()
+        for i in range(levels):
+            self._level_dims(levels, view_w, view_h, i, C.byref(w), C.byref(h))
+            out.append((w.value, h.value))
+        return out
+
+    def image_size(self, levels: int, i: int, view_w: float, view_h: float):
+        o = (C.c_float * 2)()
+        self._image_size(levels, i, view_w, view_h, o)
+        return np.array([o[0], o[1]], dtype=np.float32)
+
+    def trace(self, spheres, view, ratio, rot, pos, render_dist=1000.0, levels=0, rect=None, threads=0):
+        """Run one frame.  Returns (list of per-level float32 arrays [h,w], counters dict)."""
+        sph = np.ascontiguousarray(np.asarray(spheres, dtype=np.float32).reshape(-1, 4))
+        view = np.ascontiguousarray(view, dtype=np.float32)
+        ratio = np.ascontiguousarray(ratio, dtype=np.float32)
+        rot = np.ascontiguousarray(rot, dtype=np.float32)
+        pos = np.ascontiguousarray(pos, dtype=np.float32)
+        if levels <= 0:
+            levels = self.level_count(float(view[0]))
+        dims = self.level_dims(levels, float(view[0]), float(view[1]))
+        imgs = [np.zeros((h, w), dtype=np.float32) for (w, h) in dims]
+        ptrs = (C.c_void_p * levels)(*[im.ctypes.data for im in imgs])
+        rc = None
+        if rect is not None:
+            rc = np.ascontiguousarray(rect, dtype=np.int32)
+        cnt = (C.c_ulonglong * 3)()
+        err = self._trace(sph.ctypes.data, sph.shape[0], view.ctypes.data, ratio.ctypes.data, rot.ctypes.data,
+                          pos.ctypes.data, float(render_dist), levels, rc.ctypes.data if rc is not None else None,
+                          int(threads), ptrs, cnt)
+        if err != 0:
+            raise RuntimeError(f"oracle[{self.kind}] trace failed: {err}")
+        return imgs, {"R": int(cnt[0]), "E": int(cnt[1]), "S": int(cnt[2])}
+
+
+def load(kind: str) -> Oracle:
+    if kind not in _loaded:
+        _loaded[kind] = Oracle(kind)
+    return _loaded[kind]
+
+
+def best() -> Oracle:
+    """The strongest checker present: the reference's own shader text if built, else the C port."""
+    return load("refx") if available("refx") else load("port")
+
+
+def fnv1a32(a: np.ndarray) -> str:
+    """FNV-1a-32 over the 32-bit words of a float32 image, row-major (the SURVEY.md §8c hashes)."""
+    hv = 0x811C9DC5
+    for w in np.ascontiguousarray(a, dtype=np.float32).view(np.uint32).ravel().tolist():
+        hv = ((hv ^ w) * 0x01000193) & 0xFFFFFFFF
+    return f"{hv:08x}"
+
+
+def sha256(a: np.ndarray) -> str:
+    """SHA-256 of the raw little-endian float32 bytes (fast; used by the golden fixtures)."""
+    import hashlib
+    return hashlib.sha256(np.ascontiguousarray(a, dtype="<f4").tobytes()).hexdigest()
