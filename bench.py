@@ -1,0 +1,434 @@
+#!/usr/bin/env python
+"""bench.py — the reference's headline metric (Mrays/s of the cone-march compute pass) on B200.
+
+    python bench.py --gpus 1 --steps K --warmup W            # this build (CUDA, through the C ABI)
+    python bench.py --impl reference --steps K --warmup W     # the reference's own shader on host cores
+    torchrun ... bench.py --gpus N ...                        # row-band sharded, NCCL gather to rank 0
+
+A "step" is one pass of the hot path over one batch: workload c1 (BASELINE.json configs[1]) =
+default scene, 1920x1080, 8 pyramid levels, 16 frames (the "16 spp" axis: SURVEY.md §8d) on a
+seeded camera path.  ray = one invocation of compute.glsl:main at one pyramid level.
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every definition used here.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (W, H, frames, camera path, accumulate, spheres, levels, BASELINE.json config)
+    "c1": dict(W=1920, H=1080, frames=16, path="bench", accumulate=False, scene="default", levels=0,
+               name="configs[1]: default scene 1920x1080, 8 levels, 16 frames (16 spp axis) on the seeded camera path"),
+    "c2": dict(W=3840, H=2160, frames=256, path="static", accumulate=True, scene="default", levels=0,
+               name="configs[2]: default scene 3840x2160, 9 levels, 256 frames static pose, FP32 accumulation (extension)"),
+    "c3": dict(W=1920, H=1080, frames=1, path="static", accumulate=False, scene="synthetic10k", levels=0,
+               name="configs[3]: 10,000 synthetic spheres (SplitMix64 0xB200), 1920x1080, 8 levels, 1 frame"),
+    "c4": dict(W=7680, H=4320, frames=1024, path="static", accumulate=True, scene="default", levels=0,
+               name="configs[4]: default scene 7680x4320, 10 levels (extension), 1024 frames static pose, FP32 accumulation, row bands + one gather"),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=None)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS))
+    ap.add_argument("--frames", type=int, default=None, help="override frames per step (labelled in config)")
+    ap.add_argument("--levels", type=int, default=None, help="override pyramid levels (configs[3] sweep)")
+    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 per-level kernels, 2 fused pyramid kernel")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_inputs(wl):
+    from raytracing_engine_b200 import camera, scene
+    if wl["scene"] == "default":
+        spheres = scene.spheres_of(scene.default_mutable_data())
+    else:
+        spheres = scene.synthetic_spheres(10000, seed=0xB200)
+    if wl["path"] == "bench":
+        rots, poss = camera.bench_camera_path(wl["frames"])
+    else:
+        rots, poss = camera.static_path(wl["frames"])
+    return spheres, rots, poss
+
+
+def algorithmic_ops(cnt, n_spheres):
+    """ops = 57 R + 10 E + (12 + 3 N) S  (1 op = 1 separately rounded FP32 operation)."""
+    return 57 * cnt["R"] + 10 * cnt["E"] + (12 + 3 * n_spheres) * cnt["S"]
+
+
+def algorithmic_bytes(rays_all_levels, rays_level0):
+    """4 B written per pixel of every level + 4 B read per parent texel (shared by 4 children)."""
+    return 4 * rays_all_levels + (rays_all_levels - rays_level0)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as fh:
+            d = json.load(fh)
+        return float(d.get("hbm_gbs", 6650.0)), float(d.get("sm_max_mhz", 1965.0)), "measured"
+    return 6650.0, 1965.0, "fallback"
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons of one GPU while the timed region runs (pynvml)."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self.ok = [], set(), None, False
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = int(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception:
+            self.ok = False
+        self.t = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(int(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                r = int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.01)
+
+    def start(self):
+        if self.ok:
+            self.t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self.ok:
+            self.t.join(1.0)
+        med = int(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def cpu_reference_step(wl, spheres, rots, poss, levels, frames, rect=None):
+    """One bounded sample of the workload on the host cores with the reference's own shader text
+    (oracle/_ref) when it was built, else the C port.  Returns (seconds, rays, kind, cores, oracle)."""
+    import oracle
+    from raytracing_engine_b200 import scene
+    need_ext = len(spheres) > 8 or levels > 9
+    kind = ("refx" if need_ext else "ref")
+    if not oracle.available(kind):
+        kind = "port"
+    o = oracle.load(kind)
+    cores = os.cpu_count() or 1
+    ratio = scene.view_ratio(wl["W"], wl["H"])
+    t0 = time.perf_counter()
+    rays = 0
+    for k in range(frames):
+        _, cnt = o.trace(spheres, [wl["W"], wl["H"]], ratio, rots[k], poss[k], 1000.0, levels, rect=rect, threads=cores)
+        rays += cnt["R"]
+    return time.perf_counter() - t0, rays, kind, cores, o
+
+
+def run_reference(args, wl):
+    """--impl reference: the reference's CPU-compiled shader over the same workload, host threads only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    from raytracing_engine_b200 import engine
+    spheres, rots, poss = workload_inputs(wl)
+    levels = wl["levels"] or oracle.load("port").level_count(float(wl["W"]))
+    steps = args.steps if args.steps is not None else 3
+    warmup = args.warmup if args.warmup is not None else 1
+    # bounded sample per step: at most 4 frames of the batch (each frame costs the same work +-10 %)
+    frames = min(wl["frames"], max(1, int(64e6 / (wl["W"] * wl["H"] * 1.34))))
+    rect = None
+    if wl["scene"] != "default":
+        cx, cy = wl["W"] // 2, wl["H"] // 2
+        rect = [cx - 128, cy - 72, cx + 128, cy + 72]   # centred 256x144 window for 10k spheres
+    for _ in range(warmup):
+        cpu_reference_step(wl, spheres, rots, poss, levels, frames, rect)
+    tot_t, tot_r = 0.0, 0
+    for _ in range(steps):
+        t, r, kind, cores, _o = cpu_reference_step(wl, spheres, rots, poss, levels, frames, rect)
+        tot_t += t
+        tot_r += r
+    value = tot_r / tot_t / 1e6
+    sample = f"{frames} of {wl['frames']} frames per step" + (", centred 256x144 window of every level" if rect else ", full image")
+    line = {
+        "impl": "reference", "metric": "Mrays/s (pixel-invocations of compute.glsl:main over all pyramid levels)",
+        "value": value, "unit": "Mrays/s", "n_gpus": 0, "steps": steps, "warmup": warmup,
+        "ms_per_step": tot_t / steps * 1e3 * (wl["frames"] / frames), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "levels": levels, "frames_per_step": wl["frames"]},
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores,
+                         "kind": "reference" if kind in ("ref", "refx") else "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+class _DevView:
+    """Zero-copy torch view of engine-owned device memory (CUDA array interface)."""
+
+    def __init__(self, ptr, shape, strides_bytes):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 3, "strides": tuple(strides_bytes)}
+
+
+def run_ours(args, wl):
+    import torch
+    import torch.distributed as dist
+    import raytracing_engine_b200 as rt
+    from raytracing_engine_b200 import scene, sharding
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the compute pass has no CPU fallback "
+                         "(use --impl reference for the host-core baseline)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    n_gpus = world
+
+    spheres, rots, poss = workload_inputs(wl)
+    pcs = rt.make_push_constants(rots, poss)
+    frames = wl["frames"]
+    steps = args.steps if args.steps is not None else (200 if frames * wl["W"] * wl["H"] < 1e9 else 3)
+    warmup = args.warmup if args.warmup is not None else (10 if steps >= 50 else 3)
+    warmup = max(warmup, 3)
+
+    eng = rt.Engine(local_rank, scene.RENDER_DIST)
+    stream = torch.cuda.Stream(device=local_rank)
+    eng.set_stream(stream.cuda_stream)
+    eng.set_option(rt.OPT_KERNEL, args.kernel)
+    slots = min(frames, 16)
+    eng.set_option(rt.OPT_FRAME_SLOTS, slots)
+    if len(spheres) <= 8:
+        eng.set_scene(scene.pack_mutable_data(objects=[(tuple(s[:3]), s[3]) for s in spheres]))
+    else:
+        eng.set_spheres(spheres)
+    eng.set_view(wl["W"], wl["H"], levels=wl["levels"])
+    levels = eng.levels
+    Wf, Hf, _ = eng.level_info(-1, 0)
+    y0, y1 = sharding.band_rows(Hf, world, rank)
+    if world > 1:
+        eng.set_rect(0, y0, Wf, y1)
+
+    def dev_final(nslots):
+        _, _, p0 = eng.level_info(-1, 0)
+        stride = (eng.level_info(-1, 1)[2] - p0) if nslots > 1 else Wf * Hf * 4
+        return torch.as_tensor(_DevView(p0, (nslots, Hf, Wf), (stride, Wf * 4, 4)), device=f"cuda:{local_rank}")
+
+    def step():
+        """One pass of the hot path over the batch, inputs resident; N>1: + the one gather to rank 0."""
+        if wl["accumulate"]:
+            eng.trace_accumulate(pcs)
+            if world > 1:
+                w_, h_, p = eng.lib, None, None
+                import ctypes as C
+                pw, ph, pp = C.c_int(), C.c_int(), C.c_void_p()
+                eng._check(eng.lib.rtce_accum_info(eng._ctx, C.byref(pw), C.byref(ph), C.byref(pp)), "rtce_accum_info")
+                acc = torch.as_tensor(_DevView(pp.value, (1, Hf, Wf), (Wf * Hf * 4, Wf * 4, 4)), device=f"cuda:{local_rank}")
+                return sharding.gather_bands(acc[:, y0:y1, :], Hf, dst=0)
+        else:
+            eng.trace(pcs)
+            if world > 1:
+                return sharding.gather_bands(dev_final(slots)[:, y0:y1, :], Hf, dst=0)
+        return None
+
+    # ---- work counters of one step (separate counted run; also the parity spot-check input) ----
+    with torch.cuda.stream(stream):
+        eng.set_option(rt.OPT_COUNTERS, 1)
+        if wl["accumulate"]:
+            eng.trace_accumulate(pcs[: min(frames, slots)])
+        else:
+            eng.trace(pcs[: min(frames, slots)])
+        cnt = eng.counters()
+        eng.set_option(rt.OPT_COUNTERS, 0)
+    scale = frames / min(frames, slots)   # static-pose workloads repeat the same frames
+    cnt_step = {k: int(cnt[k] * scale) for k in "RES"}
+    if world > 1:
+        t = torch.tensor([cnt_step["R"], cnt_step["E"], cnt_step["S"]], dtype=torch.int64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t)
+        cnt_step = dict(zip("RES", [int(v) for v in t.tolist()]))
+    dims = rt.host_level_dims(levels, wl["W"], wl["H"])
+    rays_full_frame = sum(w * h for w, h in dims)
+    units_per_step = rays_full_frame * frames          # rays of the WHOLE job (all ranks)
+    ops_step = algorithmic_ops(cnt_step, len(spheres))
+    bytes_step = algorithmic_bytes(rays_full_frame, dims[0][0] * dims[0][1]) * frames
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    with torch.cuda.stream(stream):
+        for _ in range(warmup):
+            step()
+        barrier()
+        eng.set_option(rt.OPT_COUNTERS, 0)
+        launches0 = 0
+        sampler = ClockSampler(local_rank if "CUDA_VISIBLE_DEVICES" not in os.environ else
+                               int(os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local_rank]))
+        sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            step()
+        e1.record(stream)
+        barrier()
+        ms_total = e0.elapsed_time(e1)
+        launches_per_step = eng.counters()["launches"]
+        # keep the GPU under the same load long enough for the sampler to see clocks (not timed)
+        t_end = time.perf_counter() + max(0.0, 1.0 - ms_total * 1e-3)
+        while time.perf_counter() < t_end:
+            step()
+            torch.cuda.synchronize()
+        clocks = sampler.stop()
+    if world > 1:
+        t = torch.tensor([ms_total], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / steps
+    value = units_per_step / (ms_step * 1e-3) / 1e6
+
+    # ---- end to end through the public API with HOST buffers (push constants in, images out) ----
+    e2e = None
+    if not args.no_e2e:
+        band = y1 - y0
+        if wl["accumulate"]:
+            host = np.empty((Hf, Wf), dtype=np.float32)
+            def e2e_step():
+                eng.trace_accumulate(pcs)
+                return eng.readback_accum()
+            d2h = Wf * band * 4
+        else:
+            pin = rt.PinnedBuffer((frames, Hf, Wf))
+            def e2e_step():
+                eng.render_to_host(pcs, pin.array)
+            d2h = frames * Wf * band * 4
+        k_e2e = max(3, min(steps, int(2.0 / max(ms_step * 1e-3 * 8, 1e-4))))
+        with torch.cuda.stream(stream):
+            for _ in range(3):
+                e2e_step()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(k_e2e):
+                e2e_step()
+            barrier()
+            dt = (time.perf_counter() - t0) / k_e2e
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device=f"cuda:{local_rank}")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+            tb = torch.tensor([d2h], dtype=torch.int64, device=f"cuda:{local_rank}")
+            dist.all_reduce(tb)
+            d2h = int(tb.item())
+        e2e = {"value": units_per_step / dt / 1e6, "unit": "Mrays/s", "ms_per_step": dt * 1e3,
+               "h2d_bytes_per_step": int(pcs.nbytes) * world, "d2h_bytes_per_step": int(d2h), "steps": k_e2e,
+               "note": "host PushConstantData in (passed by value into kernel parameters), every frame's final level "
+                       "copied to pinned host memory (accumulate workloads: the one accumulated image); N>1: each rank "
+                       "returns its row band to the host"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    hbm_peak, sm_max, peak_src = measured_peaks()
+    fp32_peak, fp32_ms = rt.measure_fp32_issue(local_rank, 4096)
+    nominal = 148 * 128 * sm_max * 1e6
+    achieved = ops_step / (ms_step * 1e-3)
+    roofline = {
+        "bound": "fp32_issue", "achieved": achieved / 1e12, "peak": fp32_peak * n_gpus / 1e12, "unit": "Tlane-op/s",
+        "frac": achieved / (fp32_peak * n_gpus), "traffic": None,
+        "peak_source": "measured live: rtce_measure_fp32_issue (non-contracted FMUL/FADD, register operands); "
+                       f"nominal 148 SM x 128 lanes x {sm_max:.0f} MHz = {nominal / 1e12:.1f}",
+        "frac_of_nominal": achieved / (nominal * n_gpus),
+        "ops_per_step": ops_step, "counters_per_step": cnt_step,
+        "scope": "all kernels of the step (launch gaps included)",
+        "hbm": {"achieved": bytes_step / (ms_step * 1e-3) / 1e9, "peak": hbm_peak * n_gpus, "unit": "GB/s",
+                "frac": bytes_step / (ms_step * 1e-3) / 1e9 / (hbm_peak * n_gpus), "peak_source": peak_src + " MEASURED_PEAKS.json",
+                "bytes_per_step": bytes_step},
+    }
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline and n_gpus == 1:
+        rect = None
+        f_cpu = min(frames, max(1, int(64e6 / (wl["W"] * wl["H"] * 1.34))))
+        if len(spheres) > 8:
+            cx, cy = wl["W"] // 2, wl["H"] // 2
+            rect = [cx - 128, cy - 72, cx + 128, cy + 72]
+        cpu_reference_step(wl, spheres, rots, poss, levels, 1, rect)   # warm the threads
+        best, rays_cpu = 1e30, 0
+        for _ in range(3):
+            t, r, kind, cores, _o = cpu_reference_step(wl, spheres, rots, poss, levels, f_cpu, rect)
+            if t < best:
+                best, rays_cpu = t, r
+        cpu_baseline = {"value": rays_cpu / best / 1e6, "unit": "Mrays/s", "cores": cores,
+                        "kind": "reference" if kind in ("ref", "refx") else "port",
+                        "sample": f"{f_cpu} of {frames} frames" + (", centred 256x144 window of every level" if rect else ", full image")
+                                  + ", best of 3, OpenMP over rows"}
+
+    line = {
+        "metric": "Mrays/s (pixel-invocations of compute.glsl:main over all pyramid levels)",
+        "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": steps, "warmup": warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if n_gpus > 1 else "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": wl["name"], "levels": levels, "frames_per_step": frames,
+                   "rays_per_step": units_per_step, "primary_rays_per_step": Wf * Hf * frames,
+                   "ms_per_frame": ms_step / frames,
+                   "parallelism": "1 GPU" if n_gpus == 1 else f"{n_gpus} row bands of the final level + one NCCL gather to rank 0 per step",
+                   "l2": f"no flush: each step rewrites {bytes_step / 1e6:.0f} MB of pyramid (> 126 MB L2 when frames >= 12 at 1080p); parents are meant to be L2 hits",
+                   "kernel": {0: "auto", 1: "per-level", 2: "fused"}[args.kernel]},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps),
+        "roofline": roofline, "cpu_baseline": cpu_baseline,
+        "mprimary_per_s": Wf * Hf * frames / (ms_step * 1e-3) / 1e6,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    wl = dict(WORKLOADS[args.workload])
+    if args.frames:
+        wl["frames"] = args.frames
+        wl["name"] += f" [frames overridden to {args.frames}]"
+    if args.levels:
+        wl["levels"] = args.levels
+        wl["name"] += f" [levels overridden to {args.levels}]"
+    if args.impl == "reference":
+        run_reference(args, wl)
+        return
+    run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

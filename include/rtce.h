@@ -1,0 +1,165 @@
+/* rtce.h — C ABI of the B200-native cone-march compute pass.
+ *
+ * Drop-in boundary for ONE path of IvoteSligte/raytracing_engine: the per-pixel
+ * compute pass (shaders/compute.glsl + shaders/utilities.glsl) and the host loop
+ * that drives it (src/main.rs:291-316).  The reference has no FFI of its own;
+ * the pass sits behind a Vulkan bind-and-dispatch sequence, so every entry
+ * point below names the Vulkan-side code it replaces (file:line under the
+ * reference tree).  Byte layouts are the reference's own (std140 / push-constant
+ * layouts generated from the shaders, src/main.rs:47-66).
+ *
+ * Conventions: every function returns RTCE_OK (0) or a negative rtce_status and
+ * never unwinds across the ABI (the reference's convention is unwrap()-panic —
+ * src/main.rs:91,166,315 — a Rust wrapper maps codes to Result).  Host buffers
+ * are owned by the caller and copied during the call; device memory is owned by
+ * the context.  A context is bound to one CUDA device and one stream, is NOT
+ * thread-safe (the reference is one host thread and one queue, main.rs:460,721),
+ * and work is asynchronous until rtce_sync / rtce_readback*.  There is no CPU
+ * fallback: without a CUDA device rtce_create fails with RTCE_ERR_CUDA.
+ */
+#ifndef RTCE_H
+#define RTCE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTCE_ABI_VERSION 1
+
+/* limits of the reference shader (utilities.glsl:1-3, compute.glsl:14-15, main.rs:359) */
+#define RTCE_REF_MAX_OBJECTS 8
+#define RTCE_REF_MAX_LEVELS 9
+/* limits of this build (SURVEY.md finding 4: both caps are lifted by parameterising the same algorithm) */
+#define RTCE_MAX_LEVELS 16
+#define RTCE_MAX_SPHERES 16384
+
+typedef enum rtce_status {
+    RTCE_OK = 0,
+    RTCE_ERR_INVALID = -1,   /* bad argument (null pointer, size, range) */
+    RTCE_ERR_CUDA = -2,      /* CUDA runtime error; see rtce_last_error */
+    RTCE_ERR_STATE = -3,     /* call order: scene / view not set yet */
+    RTCE_ERR_LIMIT = -4,     /* exceeds RTCE_MAX_* */
+    RTCE_ERR_NOMEM = -5
+} rtce_status;
+
+/* compute.glsl:7-12 `PushConstantData` — 40 bytes, filled at main.rs:301-307, 624-629, 770-773.
+ * rot = glam Quat::to_array() = [x, y, z, w].  `iter` and `imageSize` are per-level values the
+ * host loop writes (main.rs:301-307); rtce_trace* ignore the caller's and fill them per level. */
+typedef struct rtce_push_constants {
+    float rot[4];        /* @0  */
+    float pos[3];        /* @16 */
+    uint32_t iter;       /* @28 */
+    float imageSize[2];  /* @32 */
+} rtce_push_constants;
+
+/* compute.glsl:26-29 `ConstantBuffer` — 16 bytes, built at main.rs:608-611 / 800-803:
+ * view = window size in pixels as f32, ratio = [FOV, FOV * H / W]. */
+typedef struct rtce_constant_buffer {
+    float view[2];   /* @0 */
+    float ratio[2];  /* @8 */
+} rtce_constant_buffer;
+
+/* utilities.glsl:16-19 `Object` — one std140 array element of MutableData.objs (16 bytes). */
+typedef struct rtce_sphere {
+    float pos[3];
+    float size;
+} rtce_sphere;
+
+/* compute.glsl:17-24 `MutableData` (std140, 656 bytes), built at main.rs:524-605.
+ * matCount@0 objCount@4 lightCount@8 | mats[8]@16 stride 32 | objs[8]@272 stride 16 |
+ * lights[8]@400 stride 32.  The compute pass reads objCount and objs only. */
+#define RTCE_MUTABLE_DATA_SIZE 656
+#define RTCE_MUTABLE_DATA_OBJCOUNT_OFFSET 4
+#define RTCE_MUTABLE_DATA_OBJS_OFFSET 272
+
+typedef struct rtce_ctx rtce_ctx;
+
+/* Work counters of the last rtce_trace* call: R = rays (pixel-invocations over
+ * all levels), E = sphereSDF evaluations, S = march-loop iterations; kernel_launches = CUDA
+ * kernels this library launched.  Only filled when rtce_set_option(RTCE_OPT_COUNTERS, 1). */
+typedef struct rtce_counters {
+    uint64_t rays;
+    uint64_t sdf_evals;
+    uint64_t march_steps;
+    uint64_t kernel_launches;
+} rtce_counters;
+
+typedef enum rtce_option {
+    RTCE_OPT_COUNTERS = 1,      /* 0/1: count R/E/S on the device (slower kernels; off by default) */
+    RTCE_OPT_FRAME_SLOTS = 2,   /* frames traced concurrently by rtce_trace_batch (pyramid replicas), default 16 */
+    RTCE_OPT_KERNEL = 3         /* 0 = auto, 1 = per-level kernels, 2 = fused-pyramid kernel */
+} rtce_option;
+
+/* -- lifetime ------------------------------------------------------------------------------
+ * Replaces device/queue selection and compute-pipeline creation with its specialization
+ * constant RENDER_DIST (main.rs:68-92, 154-167, 450-460, 631-637; compute.glsl:32). */
+int rtce_create(int device, float render_dist, rtce_ctx** out);
+void rtce_destroy(rtce_ctx* ctx);
+int rtce_abi_version(void);
+const char* rtce_last_error(const rtce_ctx* ctx);   /* valid until the next call on ctx */
+const char* rtce_status_string(int status);
+int rtce_set_option(rtce_ctx* ctx, int option, int64_t value);
+/* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the context's own stream). */
+int rtce_set_stream(rtce_ctx* ctx, void* cuda_stream);
+
+/* -- scene (binding 1) ------------------------------------------------------------------------
+ * Replaces DeviceLocalBuffer::from_data(mutable_data) (main.rs:592-605).  Takes the exact
+ * 656-byte std140 image of `MutableData`. */
+int rtce_set_scene(rtce_ctx* ctx, const void* mutable_data_std140, size_t nbytes);
+/* Extension for objCount > 8 (BASELINE.json configs[3]): n spheres as {x,y,z,size}. */
+int rtce_set_spheres(rtce_ctx* ctx, const rtce_sphere* spheres, uint32_t n);
+
+/* -- view (binding 2 + binding 0) -----------------------------------------------------------
+ * Replaces the ConstantBuffer upload (main.rs:608-615, 800-834), the level count
+ * (main.rs:639; levels = 0 -> floor rule, levels = -1 -> the resize rule main.rs:845) and
+ * get_compute_images (main.rs:203-234): allocates the r32f pyramid. */
+int rtce_set_view(rtce_ctx* ctx, const rtce_constant_buffer* cb, int levels);
+/* Multi-GPU / windowing extension: restrict work to final-level rows [y0, y1) and columns
+ * [x0, x1) plus their ancestor chain on the coarser levels.  All zero = whole image. */
+int rtce_set_rect(rtce_ctx* ctx, int x0, int y0, int x1, int y1);
+int rtce_level_count(const rtce_ctx* ctx);
+/* Level `level` of frame slot `slot`: size and device pointer (row-major f32, pitch = w). */
+int rtce_level_info(const rtce_ctx* ctx, int level, int slot, int* w, int* h, float** device_ptr);
+/* Host mirrors of the pyramid arithmetic, usable without a context or a GPU. */
+int rtce_host_level_count(float view_w, int resize_rule);                               /* main.rs:639 / 845 */
+int rtce_host_level_dims(int levels, float view_w, float view_h, int level, int* w, int* h); /* main.rs:209-213 */
+int rtce_host_image_size(int levels, int level, float view_w, float view_h, float out[2]);   /* main.rs:303-305 */
+
+/* -- the pass ---------------------------------------------------------------------------------
+ * Replaces get_command_buffer's compute half + queue submit (main.rs:291-316, 909-914): for each
+ * pyramid level, push constants {iter, imageSize}, dispatch over the level image.  One frame into
+ * slot 0, or `frames` frames (frame k into slot k % slots).  Asynchronous. */
+int rtce_trace(rtce_ctx* ctx, const rtce_push_constants* pc);
+int rtce_trace_batch(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
+/* Extension ("progressive accumulation"): trace `frames` frames and keep only the
+ * running FP32 sum of their final levels, divided by `frames` at the end, in an internal image. */
+int rtce_trace_accumulate(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
+int rtce_accum_info(const rtce_ctx* ctx, int* w, int* h, float** device_ptr);
+
+/* -- consumers of binding 0 (main.rs:650-655 -> fragment.glsl:15,135) ---------------------------
+ * Headless readback; both synchronise.  pitch_bytes = 0 -> tightly packed rows. */
+int rtce_readback(rtce_ctx* ctx, int level, int slot, float* host, size_t pitch_bytes);
+int rtce_readback_accum(rtce_ctx* ctx, float* host, size_t pitch_bytes);
+/* End-to-end convenience used by headless callers: trace `frames` frames from HOST push constants
+ * and copy every frame's final level to `host_out` (frames * w * h floats), copies overlapped
+ * with the tracing of later frames.  Synchronises before returning. */
+int rtce_render_to_host(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames, float* host_out);
+/* Page-locked host buffers for rtce_render_to_host / rtce_readback (pageable memory works, slower). */
+int rtce_host_alloc(void** out, size_t nbytes);
+int rtce_host_free(void* p);
+int rtce_sync(rtce_ctx* ctx);                        /* fence wait, main.rs:882-884 */
+int rtce_get_counters(rtce_ctx* ctx, rtce_counters* out);
+
+/* -- measurement support (no reference counterpart) ---------------------------------------------
+ * Sustained FP32 CUDA-core issue rate of `device`: a register-only kernel of independent,
+ * non-contracted FMUL/FADD chains, timed with CUDA events.  Writes lane-operations per second
+ * (the denominator of the FP32-issue roofline) and the kernel time in ms. */
+int rtce_measure_fp32_issue(int device, int iters, double* lane_ops_per_s, double* ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTCE_H */

@@ -97,34 +97,39 @@ RTCE_EXPORT int RTCE_FN(_trace)(const float* spheres, uint32_t n, const float* v
     }
 
     unsigned long long R = 0, E = 0, M = 0;
-    // the pass loop, main.rs:300-316 (the per-level clear at :312 is dropped: every texel in range is overwritten)
-    for (int i = 0; i < levels; i++) {
-        float isz[2];
-        rtce_hm_image_size(levels, i, view2[0], view2[1], isz);
-        pc.iter = (uint)i;
-        pc.imageSize = vec2(isz[0], isz[1]);
-        int rc[4];
-        rtce_hm_level_rect(levels, i, rect4, lw[i], lh[i], rc);
-        const int x0 = rc[0], y0 = rc[1], x1 = rc[2], y1 = rc[3];
+    int rc[4] = {0, 0, 0, 0};
+    // the pass loop, main.rs:300-316 (the per-level clear at :312 is dropped: every texel in range is
+    // overwritten).  One thread team for the whole frame; the barrier after each level is the image
+    // barrier vulkano inserts between dispatches (level i reads image i-1, compute.glsl:81).
 #pragma omp parallel num_threads(threads) reduction(+ : R, E, M)
-        {
+    {
 #ifdef RTCE_COUNT
-            rtce_cnt_distance = 0;
-            rtce_cnt_max = 0;
+        rtce_cnt_distance = 0;
+        rtce_cnt_max = 0;
 #endif
-#pragma omp for schedule(dynamic, 4)
+        for (int i = 0; i < levels; i++) {
+#pragma omp single
+            {
+                float isz[2];
+                rtce_hm_image_size(levels, i, view2[0], view2[1], isz);
+                pc.iter = (uint)i;
+                pc.imageSize = vec2(isz[0], isz[1]);
+                rtce_hm_level_rect(levels, i, rect4, lw[i], lh[i], rc);
+            }   // implicit barrier
+            const int x0 = rc[0], y0 = rc[1], x1 = rc[2], y1 = rc[3];
+#pragma omp for schedule(dynamic, 1)
             for (int y = y0; y < y1; y++) {
                 for (int x = x0; x < x1; x++) {
                     gl_GlobalInvocationID = uvec3((uint)x, (uint)y, 0u);   // dispatch([w/8,h/8,1]) x local 8x8
                     rtce_ref_shader_main();
                 }
                 R += (unsigned long long)(x1 - x0);
-            }
-#ifdef RTCE_COUNT
-            E += rtce_cnt_distance;
-            M += rtce_cnt_max;
-#endif
+            }   // implicit barrier
         }
+#ifdef RTCE_COUNT
+        E += rtce_cnt_distance;
+        M += rtce_cnt_max;
+#endif
     }
     if (counters3) {
         counters3[0] = R;

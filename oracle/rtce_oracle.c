@@ -147,21 +147,26 @@ RTCE_EXPORT int rtce_oracle_trace(const float* spheres, uint32_t n, const float*
 
     unsigned long long R = 0, E = 0, S = 0;
     int fail = 0;
-    for (int i = 0; i < levels; i++) {
-        float isz[2];
-        rtce_hm_image_size(levels, i, view2[0], view2[1], isz);
-        int rc[4];
-        rtce_hm_level_rect(levels, i, rect4, lw[i], lh[i], rc);
-        const float* parent = i > 0 ? level_out[i - 1] : NULL;
-        const int pw = i > 0 ? lw[i - 1] : 0;
-        float* out = level_out[i];
-        const int w = lw[i];
+    int rc[4] = { 0, 0, 0, 0 };
+    float isz[2] = { 0.0f, 0.0f };
+    /* One thread team per frame; the barrier that ends each level's loop is the image barrier
+     * between dispatches (level i reads image i-1, compute.glsl:81). */
 #pragma omp parallel num_threads(threads) reduction(+ : R, E, S) reduction(| : fail)
-        {
-            float* distances = (float*)malloc(sizeof(float) * (n ? n : 1));
-            counters_t cnt = { 0, 0 };
-            if (!distances) fail = 1;
-#pragma omp for schedule(dynamic, 4)
+    {
+        float* distances = (float*)malloc(sizeof(float) * (n ? n : 1));
+        counters_t cnt = { 0, 0 };
+        if (!distances) fail = 1;
+        for (int i = 0; i < levels; i++) {
+#pragma omp single
+            {
+                rtce_hm_image_size(levels, i, view2[0], view2[1], isz);
+                rtce_hm_level_rect(levels, i, rect4, lw[i], lh[i], rc);
+            } /* implicit barrier */
+            const float* parent = i > 0 ? level_out[i - 1] : NULL;
+            const int pw = i > 0 ? lw[i - 1] : 0;
+            float* out = level_out[i];
+            const int w = lw[i];
+#pragma omp for schedule(dynamic, 1)
             for (int y = rc[1]; y < rc[3]; y++) {
                 if (!distances) continue;
                 for (int x = rc[0]; x < rc[2]; x++) {
@@ -170,13 +175,13 @@ RTCE_EXPORT int rtce_oracle_trace(const float* spheres, uint32_t n, const float*
                                     spheres, n, render_dist, distances, &cnt);
                 }
                 R += (unsigned long long)(rc[2] - rc[0]);
-            }
-            E += cnt.E;
-            S += cnt.S;
-            free(distances);
+            } /* implicit barrier */
         }
-        if (fail) return -5;
+        E += cnt.E;
+        S += cnt.S;
+        free(distances);
     }
+    if (fail) return -5;
     if (counters3) {
         counters3[0] = R;
         counters3[1] = E;

@@ -1,0 +1,14 @@
+"""raytracing_engine_b200 — B200-native (sm_100a CUDA) build of ONE path of
+IvoteSligte/raytracing_engine: the per-pixel cone-march compute pass
+(shaders/compute.glsl + utilities.glsl, driven by src/main.rs:291-316).
+
+The product is the C-ABI library `librtce.so` (include/rtce.h); this package is its Python
+host-side mirror.  Nothing here imports `oracle/` and nothing computes the pass on the CPU.
+"""
+from .engine import (Engine, PinnedBuffer, RtceError, PUSH_CONSTANTS_DTYPE, make_push_constants, load_library,
+                     host_level_count, host_level_dims, host_image_size, LIB_PATH, measure_fp32_issue,
+                     OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED)
+from . import scene, camera
+
+__all__ = ["Engine", "PinnedBuffer", "RtceError", "PUSH_CONSTANTS_DTYPE", "make_push_constants", "load_library",
+           "host_level_count", "host_level_dims", "host_image_size", "scene", "camera", "LIB_PATH"]

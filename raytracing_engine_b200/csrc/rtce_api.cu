@@ -1,0 +1,320 @@
+// rtce_api.cu — the C ABI declared in include/rtce.h: context, scene / view state, the level
+// loop of src/main.rs:291-316 expressed as kernel launches, and headless readback.
+// No CPU fallback exists anywhere in this file: every compute entry point launches CUDA kernels.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/rtce.h"
+#include "rtce_host.hpp"
+#include "rtce_kernels.cuh"
+
+using namespace rtce;
+
+struct rtce_ctx {
+    int device = 0;
+    float render_dist = 1000.0f;
+    cudaStream_t own_stream = nullptr;   // created by rtce_create
+    cudaStream_t stream = nullptr;       // the stream work is issued on (own_stream or the caller's)
+    cudaStream_t copy_stream = nullptr;  // D2H copies of rtce_render_to_host
+    cudaEvent_t ev_traced[2] = {nullptr, nullptr};
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr};
+    std::string err;
+
+    // binding 1 (MutableData.objCount / objs)
+    bool have_scene = false;
+    int n_spheres = 0;
+    float4 small[kSmallSceneMax];
+    float4* d_spheres = nullptr;   // objCount > 8 only
+    size_t d_spheres_cap = 0;
+
+    // binding 2 (ConstantBuffer) + binding 0 (the pyramid)
+    bool have_view = false;
+    rtce_constant_buffer cb{};
+    int levels = 0;
+    int lw[kMaxLevels]{}, lh[kMaxLevels]{};
+    size_t loff[kMaxLevels]{};   // float offset of each level inside one slot
+    size_t slot_stride = 0;      // floats per slot (all levels, 256-byte aligned each)
+    int slots = 16;
+    int slots_alloc = 0;
+    float* d_pyr = nullptr;
+    size_t d_pyr_floats = 0;
+    int rect[4] = {0, 0, 0, 0};
+    float* d_accum = nullptr;
+    size_t d_accum_floats = 0;
+
+    // options / counters
+    bool count = false;
+    int kernel_mode = 0;
+    unsigned long long* d_counters = nullptr;
+    uint64_t launches = 0;
+};
+
+namespace {
+
+int fail(rtce_ctx* c, int code, const char* what, cudaError_t e = cudaSuccess) {
+    if (c) {
+        c->err = what;
+        if (e != cudaSuccess) {
+            c->err += ": ";
+            c->err += cudaGetErrorString(e);
+        }
+    }
+    return code;
+}
+
+#define RTCE_CUDA(c, call)                                            \
+    do {                                                              \
+        cudaError_t e_ = (call);                                      \
+        if (e_ != cudaSuccess) return fail((c), RTCE_ERR_CUDA, #call, e_); \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+int ensure_pyramid(rtce_ctx* c) {
+    const size_t need = c->slot_stride * (size_t)c->slots;
+    if (c->d_pyr && c->d_pyr_floats >= need && c->slots_alloc >= c->slots) return RTCE_OK;
+    if (c->d_pyr) {
+        RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+        RTCE_CUDA(c, cudaFree(c->d_pyr));
+        c->d_pyr = nullptr;
+    }
+    cudaError_t e = cudaMalloc(&c->d_pyr, need * sizeof(float));
+    if (e != cudaSuccess) return fail(c, RTCE_ERR_NOMEM, "cudaMalloc(pyramid)", e);
+    c->d_pyr_floats = need;
+    c->slots_alloc = c->slots;
+    // the reference clears every level image before its dispatch (main.rs:312); texels outside a
+    // set rect are never written by the pass, so clear once here to give them the same value
+    RTCE_CUDA(c, cudaMemsetAsync(c->d_pyr, 0, need * sizeof(float), c->stream));
+    return RTCE_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtce_abi_version(void) { return RTCE_ABI_VERSION; }
+
+const char* rtce_status_string(int s) {
+    switch (s) {
+        case RTCE_OK: return "ok";
+        case RTCE_ERR_INVALID: return "invalid argument";
+        case RTCE_ERR_CUDA: return "CUDA error";
+        case RTCE_ERR_STATE: return "scene or view not set";
+        case RTCE_ERR_LIMIT: return "limit exceeded";
+        case RTCE_ERR_NOMEM: return "out of device memory";
+        default: return "unknown status";
+    }
+}
+
+const char* rtce_last_error(const rtce_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int rtce_create(int device, float render_dist, rtce_ctx** out) {
+    if (!out) return RTCE_ERR_INVALID;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev <= 0) return RTCE_ERR_CUDA;   // no GPU: there is no fallback
+    if (device < 0 || device >= ndev) return RTCE_ERR_INVALID;
+    rtce_ctx* c = new (std::nothrow) rtce_ctx();
+    if (!c) return RTCE_ERR_NOMEM;
+    c->device = device;
+    c->render_dist = render_dist;
+    DeviceGuard g(device);
+    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long)) != cudaSuccess) {
+        rtce_destroy(c);
+        return RTCE_ERR_CUDA;
+    }
+    for (int i = 0; i < 2; i++) {
+        cudaEventCreateWithFlags(&c->ev_traced[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming);
+    }
+    c->stream = c->own_stream;
+    *out = c;
+    return RTCE_OK;
+}
+
+void rtce_destroy(rtce_ctx* c) {
+    if (!c) return;
+    DeviceGuard g(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+    for (int i = 0; i < 2; i++) {
+        if (c->ev_traced[i]) cudaEventDestroy(c->ev_traced[i]);
+        if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
+    }
+    if (c->d_pyr) cudaFree(c->d_pyr);
+    if (c->d_accum) cudaFree(c->d_accum);
+    if (c->d_spheres) cudaFree(c->d_spheres);
+    if (c->d_counters) cudaFree(c->d_counters);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    delete c;
+}
+
+int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
+    if (!c) return RTCE_ERR_INVALID;
+    switch (option) {
+        case RTCE_OPT_COUNTERS: c->count = value != 0; return RTCE_OK;
+        case RTCE_OPT_FRAME_SLOTS:
+            if (value < 1 || value > 4096) return fail(c, RTCE_ERR_INVALID, "frame slots out of range");
+            c->slots = (int)value;
+            if (c->have_view) {
+                DeviceGuard g(c->device);
+                return ensure_pyramid(c);
+            }
+            return RTCE_OK;
+        case RTCE_OPT_KERNEL:
+            if (value < 0 || value > 2) return fail(c, RTCE_ERR_INVALID, "kernel mode out of range");
+            c->kernel_mode = (int)value;
+            return RTCE_OK;
+        default: return fail(c, RTCE_ERR_INVALID, "unknown option");
+    }
+}
+
+int rtce_set_stream(rtce_ctx* c, void* cuda_stream) {
+    if (!c) return RTCE_ERR_INVALID;
+    DeviceGuard g(c->device);
+    RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+    return RTCE_OK;
+}
+
+int rtce_set_spheres(rtce_ctx* c, const rtce_sphere* spheres, uint32_t n) {
+    if (!c || (n && !spheres)) return fail(c, RTCE_ERR_INVALID, "rtce_set_spheres: null");
+    if (n > RTCE_MAX_SPHERES) return fail(c, RTCE_ERR_LIMIT, "rtce_set_spheres: n > RTCE_MAX_SPHERES");
+    DeviceGuard g(c->device);
+    c->n_spheres = (int)n;
+    memset(c->small, 0, sizeof(c->small));
+    if (n <= (uint32_t)kSmallSceneMax) {
+        for (uint32_t i = 0; i < n; i++)
+            c->small[i] = make_float4(spheres[i].pos[0], spheres[i].pos[1], spheres[i].pos[2], spheres[i].size);
+    } else {
+        if (c->d_spheres_cap < n) {
+            if (c->d_spheres) {
+                RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+                RTCE_CUDA(c, cudaFree(c->d_spheres));
+                c->d_spheres = nullptr;
+            }
+            cudaError_t e = cudaMalloc(&c->d_spheres, sizeof(float4) * (size_t)n);
+            if (e != cudaSuccess) return fail(c, RTCE_ERR_NOMEM, "cudaMalloc(spheres)", e);
+            c->d_spheres_cap = n;
+        }
+        // rtce_sphere is {x,y,z,size} = the float4 layout; pageable source -> staged copy completes before return
+        RTCE_CUDA(c, cudaMemcpyAsync(c->d_spheres, spheres, sizeof(float4) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+        RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    c->have_scene = true;
+    return RTCE_OK;
+}
+
+int rtce_set_scene(rtce_ctx* c, const void* md, size_t nbytes) {
+    if (!c || !md) return fail(c, RTCE_ERR_INVALID, "rtce_set_scene: null");
+    if (nbytes != RTCE_MUTABLE_DATA_SIZE) return fail(c, RTCE_ERR_INVALID, "rtce_set_scene: MutableData is 656 bytes (std140)");
+    const unsigned char* b = (const unsigned char*)md;
+    uint32_t n = 0;
+    memcpy(&n, b + RTCE_MUTABLE_DATA_OBJCOUNT_OFFSET, 4);
+    // the shader indexes objs[i] for i < objCount with objs[MAX_OBJECTS]; more than 8 is out of bounds there
+    if (n > RTCE_REF_MAX_OBJECTS) return fail(c, RTCE_ERR_LIMIT, "rtce_set_scene: objCount > MAX_OBJECTS (8)");
+    rtce_sphere s[RTCE_REF_MAX_OBJECTS];
+    memcpy(s, b + RTCE_MUTABLE_DATA_OBJS_OFFSET, sizeof(s));
+    return rtce_set_spheres(c, s, n);
+}
+
+int rtce_host_level_count(float view_w, int resize_rule) { return host_level_count(view_w, resize_rule != 0); }
+
+int rtce_host_level_dims(int levels, float vw, float vh, int level, int* w, int* h) {
+    if (!w || !h || levels < 1 || levels > RTCE_MAX_LEVELS || level < 0 || level >= levels) return RTCE_ERR_INVALID;
+    host_level_dims(levels, vw, vh, level, w, h);
+    return RTCE_OK;
+}
+
+int rtce_host_image_size(int levels, int level, float vw, float vh, float out[2]) {
+    if (!out || levels < 1 || levels > RTCE_MAX_LEVELS || level < 0 || level >= levels) return RTCE_ERR_INVALID;
+    host_image_size(levels, level, vw, vh, out);
+    return RTCE_OK;
+}
+
+int rtce_set_view(rtce_ctx* c, const rtce_constant_buffer* cb, int levels) {
+    if (!c || !cb) return fail(c, RTCE_ERR_INVALID, "rtce_set_view: null");
+    if (!(cb->view[0] >= 1.0f) || !(cb->view[1] >= 1.0f)) return fail(c, RTCE_ERR_INVALID, "rtce_set_view: view < 1");
+    if (levels == 0) levels = host_level_count(cb->view[0], false);
+    else if (levels == -1) levels = host_level_count(cb->view[0], true);
+    if (levels < 1) return fail(c, RTCE_ERR_INVALID, "rtce_set_view: levels");
+    if (levels > RTCE_MAX_LEVELS) return fail(c, RTCE_ERR_LIMIT, "rtce_set_view: levels > RTCE_MAX_LEVELS");
+    DeviceGuard g(c->device);
+    size_t off = 0;
+    int lw[kMaxLevels], lh[kMaxLevels];
+    size_t loff[kMaxLevels];
+    for (int i = 0; i < levels; i++) {
+        host_level_dims(levels, cb->view[0], cb->view[1], i, &lw[i], &lh[i]);
+        if (lw[i] <= 0 || lh[i] <= 0) return fail(c, RTCE_ERR_INVALID, "rtce_set_view: empty level");
+        loff[i] = off;
+        off += ((size_t)lw[i] * (size_t)lh[i] + 63) & ~(size_t)63;   // 256-byte aligned levels
+    }
+    c->cb = *cb;
+    c->levels = levels;
+    memcpy(c->lw, lw, sizeof(lw));
+    memcpy(c->lh, lh, sizeof(lh));
+    memcpy(c->loff, loff, sizeof(loff));
+    const bool same = c->have_view && c->slot_stride == off;
+    c->slot_stride = off;
+    c->rect[0] = c->rect[1] = c->rect[2] = c->rect[3] = 0;
+    c->have_view = true;
+    if (!same) {
+        c->d_pyr_floats = 0;   // force re-allocation (and the clear)
+        if (c->d_pyr) {
+            RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+            RTCE_CUDA(c, cudaFree(c->d_pyr));
+            c->d_pyr = nullptr;
+        }
+    }
+    return ensure_pyramid(c);
+}
+
+int rtce_set_rect(rtce_ctx* c, int x0, int y0, int x1, int y1) {
+    if (!c) return RTCE_ERR_INVALID;
+    if (!c->have_view) return fail(c, RTCE_ERR_STATE, "rtce_set_rect: view not set");
+    const int W = c->lw[c->levels - 1], H = c->lh[c->levels - 1];
+    if (x0 == 0 && y0 == 0 && x1 == 0 && y1 == 0) {
+        c->rect[0] = c->rect[1] = c->rect[2] = c->rect[3] = 0;
+        return RTCE_OK;
+    }
+    if (x0 < 0 || y0 < 0 || x1 > W || y1 > H || x0 >= x1 || y0 >= y1) return fail(c, RTCE_ERR_INVALID, "rtce_set_rect: out of range");
+    c->rect[0] = x0; c->rect[1] = y0; c->rect[2] = x1; c->rect[3] = y1;
+    return RTCE_OK;
+}
+
+int rtce_level_count(const rtce_ctx* c) { return (c && c->have_view) ? c->levels : RTCE_ERR_STATE; }
+
+int rtce_level_info(const rtce_ctx* c, int level, int slot, int* w, int* h, float** dptr) {
+    if (!c) return RTCE_ERR_INVALID;
+    if (!c->have_view) return RTCE_ERR_STATE;
+    if (level < 0) level += c->levels;   // -1 = final level
+    if (level < 0 || level >= c->levels || slot < 0 || slot >= c->slots) return RTCE_ERR_INVALID;
+    if (w) *w = c->lw[level];
+    if (h) *h = c->lh[level];
+    if (dptr) *dptr = c->d_pyr + (size_t)slot * c->slot_stride + c->loff[level];
+    return RTCE_OK;
+}
+
+}  // extern "C"
+
+#include "rtce_api_trace.inc"

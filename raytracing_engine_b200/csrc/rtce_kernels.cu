@@ -1,0 +1,136 @@
+// rtce_kernels.cu — sm_100a kernels of the cone-march pass: per-level kernels.
+//
+//   k_trace_level_small<N>   compute.glsl:main for objCount = N <= 8, one thread per pixel,
+//                            all frames of a batch in one launch (grid.z)
+//   k_trace_level_large      objCount > 8 (extension): one CTA per ray, objects spread over
+//                            the CTA's threads, block-wide min per march step
+//
+// Arithmetic: rtce_device.cuh (canonical, non-contracted).  Built with --fmad=false as a
+// second line of defence; no -use_fast_math.
+#include "rtce_device.cuh"
+#include "rtce_kernels.cuh"
+
+namespace rtce {
+
+// ------------------------------------------------------------------------------------------
+// compute.glsl:34-68  traceCone — tracing algorithm 3, distances[] in registers (N static)
+// ------------------------------------------------------------------------------------------
+template <int N, bool COUNT>
+RTCE_DEV float trace_cone_small(float ox, float oy, float oz, float sx, float sy, float sz, float threshold,
+                                float render_dist, const float4* __restrict__ sph, unsigned& cntE, unsigned& cntS) {
+    float d[N > 0 ? N : 1];
+#pragma unroll
+    for (int i = 0; i < N; i++) {   // :37-39
+        d[i] = sphere_sdf(ox, oy, oz, sph[i].x, sph[i].y, sph[i].z, sph[i].w);
+    }
+    if (COUNT) cntE += N;
+    float len = 0.0f;    // :41
+    float last = 0.0f;   // :42
+    while (len < render_dist) {   // :44
+        const float px = fadd(ox, fmul(sx, len));   // :45
+        const float py = fadd(oy, fmul(sy, len));
+        const float pz = fadd(oz, fmul(sz, len));
+        float dist = render_dist;                              // :49
+        const float radius = fmul(fadd(len, 1.0f), threshold); // :50
+#pragma unroll
+        for (int i = 0; i < N; i++) {   // :51-57
+            d[i] = fsub(d[i], last);
+            if (d[i] <= radius) {
+                d[i] = sphere_sdf(px, py, pz, sph[i].x, sph[i].y, sph[i].z, sph[i].w);
+                if (COUNT) cntE++;
+            }
+            dist = glsl_min(dist, d[i]);
+        }
+        if (COUNT) cntS++;
+        last = glsl_max(dist, 0.0f);   // :59
+        len = fadd(len, last);         // :60
+        if (dist <= radius) {          // :62-65
+            len = fsub(len, radius);
+            break;
+        }
+    }
+    return len;   // :67
+}
+
+template <bool COUNT>
+RTCE_DEV void flush_counters(unsigned long long* counters, unsigned r, unsigned e, unsigned s) {
+    if (!COUNT) return;
+    // warp-aggregate, then one atomic per warp and counter
+    for (int o = 16; o > 0; o >>= 1) {
+        r += __shfl_down_sync(0xffffffffu, r, o);
+        e += __shfl_down_sync(0xffffffffu, e, o);
+        s += __shfl_down_sync(0xffffffffu, s, o);
+    }
+    if ((threadIdx.x + threadIdx.y * blockDim.x) % 32 == 0) {
+        atomicAdd(counters + 0, (unsigned long long)r);
+        atomicAdd(counters + 1, (unsigned long long)e);
+        atomicAdd(counters + 2, (unsigned long long)s);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// compute.glsl:70-87  main() — one thread per pixel of level P.iter, frame = blockIdx.z
+// ------------------------------------------------------------------------------------------
+constexpr int kTileX = 16, kTileY = 16;
+
+template <int N, bool COUNT>
+__global__ void __launch_bounds__(kTileX* kTileY)
+    k_trace_level_small(const __grid_constant__ LevelParams P) {
+    const int x = P.x0 + blockIdx.x * kTileX + threadIdx.x;
+    const int y = P.y0 + blockIdx.y * kTileY + threadIdx.y;
+    const int f = blockIdx.z;
+    unsigned cR = 0, cE = 0, cS = 0;
+    if (x < P.x1 && y < P.y1) {
+        const Cam& cam = P.cam[f];
+        // :71-72  normCoord = ((gid*2+1) * imageSize - 1.0) * ratio
+        const float ncx = fmul(fsub(fmul((float)(2u * (unsigned)x + 1u), P.isx), 1.0f), P.ratx);
+        const float ncy = fmul(fsub(fmul((float)(2u * (unsigned)y + 1u), P.isy), 1.0f), P.raty);
+        // :77  step = normalize(rotate(rot, vec3(nc.x, 1.0, nc.y)))
+        const Vec3 dir = normalize3(rotate_q(cam.rot[0], cam.rot[1], cam.rot[2], cam.rot[3], ncx, 1.0f, ncy));
+        // :79-82  start distance: 1.0 at level 0, else the parent texel ivec2(gid*0.5) of level iter-1
+        float len = 1.0f;
+        if (P.iter > 0) {
+            len = __ldg(P.parent + (size_t)f * P.slot_stride + (size_t)(y >> 1) * (size_t)P.pw + (size_t)(x >> 1));
+        }
+        // :84  len += traceCone(pos + step*len, step, threshold)
+        const float ox = fadd(cam.pos[0], fmul(dir.x, len));
+        const float oy = fadd(cam.pos[1], fmul(dir.y, len));
+        const float oz = fadd(cam.pos[2], fmul(dir.z, len));
+        len = fadd(len, trace_cone_small<N, COUNT>(ox, oy, oz, dir.x, dir.y, dir.z, P.threshold, P.render_dist,
+                                                   P.sph, cE, cS));
+        // :86  imageStore(max(len, 0))
+        P.out[(size_t)f * P.slot_stride + (size_t)y * (size_t)P.w + (size_t)x] = glsl_max(len, 0.0f);
+        cR = 1;
+    }
+    flush_counters<COUNT>(P.counters, cR, cE, cS);
+}
+
+template <int N>
+static cudaError_t launch_small_n(const LevelParams& p, int frames, bool count, cudaStream_t st) {
+    dim3 block(kTileX, kTileY, 1);
+    dim3 grid((unsigned)((p.x1 - p.x0 + kTileX - 1) / kTileX), (unsigned)((p.y1 - p.y0 + kTileY - 1) / kTileY),
+              (unsigned)frames);
+    if (count)
+        k_trace_level_small<N, true><<<grid, block, 0, st>>>(p);
+    else
+        k_trace_level_small<N, false><<<grid, block, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace_level_small(const LevelParams& p, int frames, bool count, cudaStream_t st) {
+    if (p.x1 <= p.x0 || p.y1 <= p.y0 || frames <= 0) return cudaSuccess;
+    switch (p.n_spheres) {
+        case 0: return launch_small_n<0>(p, frames, count, st);
+        case 1: return launch_small_n<1>(p, frames, count, st);
+        case 2: return launch_small_n<2>(p, frames, count, st);
+        case 3: return launch_small_n<3>(p, frames, count, st);
+        case 4: return launch_small_n<4>(p, frames, count, st);
+        case 5: return launch_small_n<5>(p, frames, count, st);
+        case 6: return launch_small_n<6>(p, frames, count, st);
+        case 7: return launch_small_n<7>(p, frames, count, st);
+        case 8: return launch_small_n<8>(p, frames, count, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace rtce

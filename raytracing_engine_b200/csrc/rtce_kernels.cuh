@@ -1,0 +1,63 @@
+// rtce_kernels.cuh — launch interface between the C-ABI layer (rtce_api.cu) and the kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtce {
+
+constexpr int kMaxBatch = 32;        // frames per launch (camera table lives in kernel params)
+constexpr int kSmallSceneMax = 8;    // MAX_OBJECTS of the reference shader (utilities.glsl:3)
+constexpr int kMaxLevels = 16;
+
+// Camera part of PushConstantData (compute.glsl:7-12): rot = quaternion [x,y,z,w], pos.
+struct Cam {
+    float rot[4];
+    float pos[3];
+    float pad;
+};
+
+// Everything one level-dispatch of compute.glsl:main needs, passed by value in the
+// kernel parameter (constant) bank: the per-level push constants (main.rs:301-307), the
+// ConstantBuffer ratio (main.rs:610), RENDER_DIST (compute.glsl:32), the objs[] part of
+// MutableData (compute.glsl:17-24) and the camera of every frame of the batch.
+struct LevelParams {
+    float* out;              // level image of frame slot 0
+    const float* parent;     // level-1 image of frame slot 0 (unused at level 0)
+    size_t slot_stride;      // floats between consecutive frame slots
+    unsigned long long* counters;   // {R, E, S} or nullptr
+    int w, pw;               // row pitch (= width) of this level and of the parent level
+    int x0, y0, x1, y1;      // rectangle of this level to compute
+    int iter;                // pc.iter
+    int n_spheres;
+    float isx, isy;          // pc.imageSize
+    float ratx, raty;        // cs.ratio
+    float threshold;         // 1.4142135 * 8 * imageSize.x  (compute.glsl:75)
+    float render_dist;
+    float4 sph[kSmallSceneMax];   // {pos.xyz, size}
+    Cam cam[kMaxBatch];
+};
+
+// Per-level kernel, objCount <= 8 (one thread per pixel, frames in grid.z).
+cudaError_t launch_trace_level_small(const LevelParams& p, int frames, bool count, cudaStream_t st);
+
+// Large scenes (objCount > 8): spheres in global memory, one CTA per ray.
+struct LevelParamsLarge {
+    float* out;
+    const float* parent;
+    size_t slot_stride;
+    unsigned long long* counters;
+    const float4* spheres;   // n x {pos.xyz, size}, 16-byte aligned
+    int w, pw;
+    int x0, y0, x1, y1;
+    int iter;
+    int n_spheres;
+    float isx, isy, ratx, raty, threshold, render_dist;
+    Cam cam[kMaxBatch];
+};
+cudaError_t launch_trace_level_large(const LevelParamsLarge& p, int frames, bool count, cudaStream_t st);
+
+// Accumulation extension: acc = (first ? 0 : acc) + img ; and the final scale by 1/frames.
+cudaError_t launch_accumulate(float* acc, const float* img, size_t n, bool first, cudaStream_t st);
+cudaError_t launch_scale(float* acc, size_t n, float divisor, cudaStream_t st);
+
+}  // namespace rtce

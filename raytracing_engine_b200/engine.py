@@ -1,0 +1,288 @@
+"""ctypes binding of the C ABI in include/rtce.h (librtce.so, built by build.py).
+
+This is the Python host-side mirror of the reference's caller, `get_command_buffer` +
+queue submit (src/main.rs:268-316, 909-914): set scene (binding 1), set view (binding 2 +
+the pyramid of binding 0), then trace frames from push constants.  There is NO CPU path:
+if librtce.so is missing or no CUDA device is present, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "librtce.so")
+
+RTCE_OK = 0
+OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL = 1, 2, 3
+KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED = 0, 1, 2
+
+# compute.glsl:7-12 PushConstantData, 40 bytes
+PUSH_CONSTANTS_DTYPE = np.dtype(
+    [("rot", "<f4", (4,)), ("pos", "<f4", (3,)), ("iter", "<u4"), ("imageSize", "<f4", (2,))]
+)
+assert PUSH_CONSTANTS_DTYPE.itemsize == 40
+
+EXPORTS = [
+    "rtce_abi_version", "rtce_create", "rtce_destroy", "rtce_last_error", "rtce_status_string",
+    "rtce_set_option", "rtce_set_stream", "rtce_set_scene", "rtce_set_spheres", "rtce_set_view",
+    "rtce_set_rect", "rtce_level_count", "rtce_level_info", "rtce_host_level_count",
+    "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
+    "rtce_trace_accumulate", "rtce_accum_info", "rtce_readback", "rtce_readback_accum",
+    "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_get_counters",
+    "rtce_measure_fp32_issue",
+]
+
+
+class RtceError(RuntimeError):
+    pass
+
+
+class _Counters(C.Structure):
+    _fields_ = [("rays", C.c_uint64), ("sdf_evals", C.c_uint64), ("march_steps", C.c_uint64),
+                ("kernel_launches", C.c_uint64)]
+
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Load librtce.so; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RtceError(f"{LIB_PATH} not built - run `python -m raytracing_engine_b200.build` "
+                        "(there is no CPU fallback for the compute pass)")
+    lib = C.CDLL(LIB_PATH)
+    vp, i32, f32, sz = C.c_void_p, C.c_int, C.c_float, C.c_size_t
+    sig = {
+        "rtce_abi_version": (i32, []),
+        "rtce_create": (i32, [i32, f32, C.POINTER(vp)]),
+        "rtce_destroy": (None, [vp]),
+        "rtce_last_error": (C.c_char_p, [vp]),
+        "rtce_status_string": (C.c_char_p, [i32]),
+        "rtce_set_option": (i32, [vp, i32, C.c_int64]),
+        "rtce_set_stream": (i32, [vp, vp]),
+        "rtce_set_scene": (i32, [vp, vp, sz]),
+        "rtce_set_spheres": (i32, [vp, vp, C.c_uint32]),
+        "rtce_set_view": (i32, [vp, vp, i32]),
+        "rtce_set_rect": (i32, [vp, i32, i32, i32, i32]),
+        "rtce_level_count": (i32, [vp]),
+        "rtce_level_info": (i32, [vp, i32, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(vp)]),
+        "rtce_host_level_count": (i32, [f32, i32]),
+        "rtce_host_level_dims": (i32, [i32, f32, f32, i32, C.POINTER(i32), C.POINTER(i32)]),
+        "rtce_host_image_size": (i32, [i32, i32, f32, f32, vp]),
+        "rtce_trace": (i32, [vp, vp]),
+        "rtce_trace_batch": (i32, [vp, vp, i32]),
+        "rtce_trace_accumulate": (i32, [vp, vp, i32]),
+        "rtce_accum_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(vp)]),
+        "rtce_readback": (i32, [vp, i32, i32, vp, sz]),
+        "rtce_readback_accum": (i32, [vp, vp, sz]),
+        "rtce_render_to_host": (i32, [vp, vp, i32, vp]),
+        "rtce_host_alloc": (i32, [C.POINTER(vp), sz]),
+        "rtce_host_free": (i32, [vp]),
+        "rtce_sync": (i32, [vp]),
+        "rtce_get_counters": (i32, [vp, C.POINTER(_Counters)]),
+        "rtce_measure_fp32_issue": (i32, [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def host_level_count(view_w: float, resize_rule: bool = False) -> int:
+    """main.rs:639 (startup) / main.rs:845 (after a resize)."""
+    return int(load_library().rtce_host_level_count(float(view_w), int(resize_rule)))
+
+
+def host_level_dims(levels: int, view_w: float, view_h: float):
+    """main.rs:209-213 -> [(w, h)] per level."""
+    lib = load_library()
+    out = []
+    w, h = C.c_int(), C.c_int()
+    for i in range(levels):
+        r = lib.rtce_host_level_dims(levels, float(view_w), float(view_h), i, C.byref(w), C.byref(h))
+        if r != RTCE_OK:
+            raise RtceError(f"rtce_host_level_dims: {r}")
+        out.append((w.value, h.value))
+    return out
+
+
+def host_image_size(levels: int, level: int, view_w: float, view_h: float) -> np.ndarray:
+    """main.rs:303-305."""
+    o = np.zeros(2, dtype=np.float32)
+    r = load_library().rtce_host_image_size(levels, level, float(view_w), float(view_h), o.ctypes.data)
+    if r != RTCE_OK:
+        raise RtceError(f"rtce_host_image_size: {r}")
+    return o
+
+
+def measure_fp32_issue(device: int = 0, iters: int = 4096):
+    """Sustained non-contracted FMUL/FADD rate of the device -> (lane-ops per second, kernel ms)."""
+    ops, ms = C.c_double(), C.c_double()
+    r = load_library().rtce_measure_fp32_issue(int(device), int(iters), C.byref(ops), C.byref(ms))
+    if r != RTCE_OK:
+        raise RtceError(f"rtce_measure_fp32_issue: {r}")
+    return ops.value, ms.value
+
+
+def make_push_constants(rots, poss) -> np.ndarray:
+    """Pack per-frame (rot[4] = quaternion xyzw, pos[3]) into PushConstantData records."""
+    rots = np.asarray(rots, dtype=np.float32).reshape(-1, 4)
+    poss = np.asarray(poss, dtype=np.float32).reshape(-1, 3)
+    pcs = np.zeros(rots.shape[0], dtype=PUSH_CONSTANTS_DTYPE)
+    pcs["rot"] = rots
+    pcs["pos"] = poss
+    pcs["imageSize"] = 1.0   # main.rs:624-629 initial value; overwritten per level
+    return pcs
+
+
+class PinnedBuffer:
+    """Page-locked float32 host buffer (rtce_host_alloc) exposed as a numpy array."""
+
+    def __init__(self, shape):
+        self.lib = load_library()
+        n = int(np.prod(shape))
+        p = C.c_void_p()
+        r = self.lib.rtce_host_alloc(C.byref(p), max(n, 1) * 4)
+        if r != RTCE_OK:
+            raise RtceError("rtce_host_alloc failed")
+        self.ptr = p
+        self.array = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_float)), shape=(max(n, 1),))[:n].reshape(shape)
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            self.lib.rtce_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Engine:
+    """One context = one GPU, one stream; mirrors the reference's per-frame compute recording."""
+
+    def __init__(self, device: int = 0, render_dist: float = 1000.0):
+        self.lib = load_library()
+        self._ctx = C.c_void_p()
+        r = self.lib.rtce_create(int(device), float(render_dist), C.byref(self._ctx))
+        if r != RTCE_OK:
+            raise RtceError(f"rtce_create(device={device}) failed: {self.lib.rtce_status_string(r).decode()} "
+                            "(a CUDA device is required; there is no CPU fallback)")
+        self.device = device
+        self.view = None
+        self.levels = 0
+
+    # -- plumbing --------------------------------------------------------------------------
+    def _check(self, r: int, what: str):
+        if r != RTCE_OK:
+            msg = self.lib.rtce_last_error(self._ctx)
+            raise RtceError(f"{what}: {self.lib.rtce_status_string(r).decode()} ({msg.decode() if msg else ''})")
+
+    def close(self):
+        if self._ctx:
+            self.lib.rtce_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_option(self, option: int, value: int):
+        self._check(self.lib.rtce_set_option(self._ctx, option, value), "rtce_set_option")
+
+    def set_stream(self, cuda_stream_handle: int):
+        self._check(self.lib.rtce_set_stream(self._ctx, C.c_void_p(cuda_stream_handle)), "rtce_set_stream")
+
+    # -- bindings --------------------------------------------------------------------------
+    def set_scene(self, mutable_data: bytes):
+        """Binding 1: the 656-byte std140 MutableData image (main.rs:592-605)."""
+        buf = bytes(mutable_data)
+        self._check(self.lib.rtce_set_scene(self._ctx, buf, len(buf)), "rtce_set_scene")
+
+    def set_spheres(self, spheres):
+        s = np.ascontiguousarray(np.asarray(spheres, dtype=np.float32).reshape(-1, 4))
+        self._check(self.lib.rtce_set_spheres(self._ctx, s.ctypes.data, s.shape[0]), "rtce_set_spheres")
+
+    def set_view(self, view_w: float, view_h: float, fov: float = 1.0, levels: int = 0, ratio=None):
+        """Binding 2 (main.rs:608-611: ratio = [FOV, FOV*H/W]) and the pyramid (main.rs:639-648)."""
+        w, h, fov = np.float32(view_w), np.float32(view_h), np.float32(fov)
+        if ratio is None:
+            ratio = (fov, np.float32(np.float32(fov * h) / w))
+        cb = np.array([w, h, ratio[0], ratio[1]], dtype=np.float32)
+        self._check(self.lib.rtce_set_view(self._ctx, cb.ctypes.data, int(levels)), "rtce_set_view")
+        self.view = (float(w), float(h))
+        self.ratio = (float(cb[2]), float(cb[3]))
+        self.levels = int(self.lib.rtce_level_count(self._ctx))
+
+    def set_rect(self, x0: int, y0: int, x1: int, y1: int):
+        self._check(self.lib.rtce_set_rect(self._ctx, x0, y0, x1, y1), "rtce_set_rect")
+
+    def level_info(self, level: int = -1, slot: int = 0):
+        w, h, p = C.c_int(), C.c_int(), C.c_void_p()
+        self._check(self.lib.rtce_level_info(self._ctx, level, slot, C.byref(w), C.byref(h), C.byref(p)),
+                    "rtce_level_info")
+        return w.value, h.value, p.value
+
+    # -- the pass --------------------------------------------------------------------------
+    def trace(self, pcs: np.ndarray):
+        pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
+        self._check(self.lib.rtce_trace_batch(self._ctx, pcs.ctypes.data, pcs.shape[0]), "rtce_trace_batch")
+
+    def trace_accumulate(self, pcs: np.ndarray):
+        pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
+        self._check(self.lib.rtce_trace_accumulate(self._ctx, pcs.ctypes.data, pcs.shape[0]),
+                    "rtce_trace_accumulate")
+
+    def sync(self):
+        self._check(self.lib.rtce_sync(self._ctx), "rtce_sync")
+
+    def readback(self, level: int = -1, slot: int = 0) -> np.ndarray:
+        w, h, _ = self.level_info(level, slot)
+        out = np.empty((h, w), dtype=np.float32)
+        self._check(self.lib.rtce_readback(self._ctx, level, slot, out.ctypes.data, 0), "rtce_readback")
+        return out
+
+    def readback_all_levels(self, slot: int = 0):
+        return [self.readback(i, slot) for i in range(self.levels)]
+
+    def readback_accum(self) -> np.ndarray:
+        w, h, _ = self.level_info(-1, 0)
+        out = np.empty((h, w), dtype=np.float32)
+        self._check(self.lib.rtce_readback_accum(self._ctx, out.ctypes.data, 0), "rtce_readback_accum")
+        return out
+
+    def render_to_host(self, pcs: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """Host push constants in, every frame's final level out to host memory (end-to-end call)."""
+        pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
+        w, h, _ = self.level_info(-1, 0)
+        if out is None:
+            out = np.empty((pcs.shape[0], h, w), dtype=np.float32)
+        assert out.dtype == np.float32 and out.size == pcs.shape[0] * h * w and out.flags["C_CONTIGUOUS"]
+        self._check(self.lib.rtce_render_to_host(self._ctx, pcs.ctypes.data, pcs.shape[0], out.ctypes.data),
+                    "rtce_render_to_host")
+        return out
+
+    def counters(self) -> dict:
+        c = _Counters()
+        self._check(self.lib.rtce_get_counters(self._ctx, C.byref(c)), "rtce_get_counters")
+        return {"R": int(c.rays), "E": int(c.sdf_evals), "S": int(c.march_steps),
+                "launches": int(c.kernel_launches)}

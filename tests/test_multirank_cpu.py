@@ -1,0 +1,85 @@
+"""world_size-2 gloo tests (CPU) of the multi-GPU host logic: row-band partition + the single gather.
+Each rank traces ITS band with the CPU checker (standing in for its GPU) through the same
+sharding.gather_bands the bench uses; rank 0 must hold an image bit-identical to the 1-rank image."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from raytracing_engine_b200 import sharding
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_band_rows_cover_image_in_multiples_of_8():
+    for H in (600, 1080, 2160, 4320, 48, 8, 136):
+        for world in (1, 2, 3, 4, 8):
+            bands = sharding.all_bands(H, world)
+            assert bands[0][0] == 0 and bands[-1][1] == H
+            for (a0, a1), (b0, b1) in zip(bands, bands[1:]):
+                assert a1 == b0
+            for (y0, y1) in bands:
+                assert y0 % 8 == 0 and (y1 % 8 == 0 or y1 == H)
+            sizes = [y1 - y0 for y0, y1 in bands]
+            assert max(sizes) - min(sizes) <= 8
+    assert [y1 - y0 for y0, y1 in sharding.all_bands(4320, 8)] == [544, 544, 544, 544, 536, 536, 536, 536]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, W, H, frames, q):
+    sys.path.insert(0, ROOT)
+    import oracle
+    from raytracing_engine_b200 import camera, scene
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        o = oracle.load("port")
+        sph = scene.spheres_of(scene.default_mutable_data())
+        n = o.level_count(float(W))
+        Hf = o.level_dims(n, float(W), float(H))[-1][1]
+        Wf = o.level_dims(n, float(W), float(H))[-1][0]
+        y0, y1 = sharding.band_rows(Hf, world, rank)
+        rots, poss = camera.bench_camera_path(frames)
+        local = []
+        for k in range(frames):
+            lv, _ = o.trace(sph, [W, H], scene.view_ratio(W, H), rots[k], poss[k], 1000.0, n,
+                            rect=[0, y0, Wf, y1], threads=1)
+            local.append(torch.from_numpy(lv[-1][y0:y1].copy()))
+        full = sharding.gather_bands(torch.stack(local), Hf, dst=0)
+        if rank == 0:
+            ok = True
+            for k in range(frames):
+                ref, _ = o.trace(sph, [W, H], scene.view_ratio(W, H), rots[k], poss[k], 1000.0, n, threads=1)
+                ok = ok and np.array_equal(full[k].numpy().view(np.uint32), ref[-1].view(np.uint32))
+            q.put(bool(ok))
+        else:
+            assert full is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,W,H", [(2, 320, 200), (3, 250, 130)])
+def test_banded_trace_plus_gather_is_bit_identical(world, W, H):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, W, H, 2, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True

@@ -1,0 +1,212 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (librtce.so), against
+  * the committed golden fixtures minted from the reference's own shader text (oracle/_ref), at
+    every size incl. BASELINE.json's full sizes (1080p, 4K, 8K/10 levels) via per-level SHA-256;
+  * the CPU checker on seeded random scenes / cameras (fuzz);
+  * size-independent properties (batch == single, band == full, slot independence).
+Bar: BIT-EXACT float32 images on every pyramid level (max abs error = 0, stronger than the
+north_star's <= 1e-3 / PSNR >= 60 dB), and equal work counters R / E / S.
+"""
+import numpy as np
+import pytest
+
+import oracle
+import raytracing_engine_b200 as rt
+from raytracing_engine_b200 import camera, scene
+
+pytestmark = pytest.mark.gpu
+
+MODES = [rt.KERNEL_PER_LEVEL, rt.KERNEL_FUSED]
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def _engine(case, mode=rt.KERNEL_AUTO, slots=None, count=False):
+    (name, kind, sph, W, H, levels, rot, pos, keep) = case
+    e = rt.Engine(0, 1000.0)
+    e.set_option(rt.OPT_KERNEL, mode)
+    if slots:
+        e.set_option(rt.OPT_FRAME_SLOTS, slots)
+    if count:
+        e.set_option(rt.OPT_COUNTERS, 1)
+    if len(sph) <= 8 and kind == "ref":
+        e.set_scene(scene.pack_mutable_data(objects=[(tuple(s[:3]), s[3]) for s in sph]))   # the 656-byte path
+    else:
+        e.set_spheres(sph)
+    e.set_view(W, H, levels=levels)
+    return e
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_golden_all_cases_bit_exact(mode, golden, case_table):
+    meta, imgs = golden
+    for name, case in case_table.items():
+        m = meta[name]
+        with _engine(case, mode, slots=2, count=True) as e:
+            assert e.levels == m["levels"], name
+            e.trace(rt.make_push_constants([case[6]], [case[7]]))
+            lv = e.readback_all_levels()
+            assert [[a.shape[1], a.shape[0]] for a in lv] == m["dims"], name
+            got = [oracle.sha256(a) for a in lv]
+            assert got == m["sha256"], (name, [i for i, (x, y) in enumerate(zip(got, m["sha256"])) if x != y])
+            c = e.counters()
+            assert {k: c[k] for k in "RES"} == m["counters"], name
+            if case[8]:
+                for i, a in enumerate(lv):
+                    assert np.array_equal(_bits(a), _bits(imgs[f"{name}/{i}"])), (name, i)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_fuzz_against_cpu_checker(mode):
+    """Seeded random scenes (0..8 spheres, some containing the camera), cameras and odd view sizes."""
+    o = oracle.best()
+    rs = np.random.RandomState(1234)
+    for it in range(24):
+        n = int(rs.randint(0, 9))
+        sph = np.zeros((n, 4), np.float32)
+        sph[:, :3] = rs.uniform(-12, 12, (n, 3))
+        sph[:, 3] = rs.uniform(0.1, 4.0, n)
+        W, H = int(rs.randint(9, 420)), int(rs.randint(9, 300))
+        yaw, pitch = rs.uniform(-3.2, 3.2), rs.uniform(-1.5, 1.5)
+        rot = camera.rotation(yaw, pitch)
+        pos = rs.uniform(-6, 6, 3).astype(np.float32)
+        rule = bool(it % 2)
+        levels = o.level_count(float(W), rule)
+        ref, cnt = o.trace(sph, [W, H], scene.view_ratio(W, H), rot, pos, 1000.0, levels)
+        with rt.Engine(0, 1000.0) as e:
+            e.set_option(rt.OPT_KERNEL, mode)
+            e.set_option(rt.OPT_COUNTERS, 1)
+            e.set_spheres(sph)
+            e.set_view(W, H, levels=-1 if rule else 0)
+            e.trace(rt.make_push_constants([rot], [pos]))
+            lv = e.readback_all_levels()
+            for i, (a, b) in enumerate(zip(lv, ref)):
+                assert np.array_equal(_bits(a), _bits(b)), (it, i, W, H, n, np.abs(a - b).max())
+            c = e.counters()
+            assert {k: c[k] for k in "RES"} == cnt
+
+
+def test_render_dist_parameter():
+    """RENDER_DIST is a specialization constant (compute.glsl:32); other values via the C port."""
+    o = oracle.load("port")
+    sph = scene.spheres_of(scene.default_mutable_data())
+    for rd in (50.0, 12.5):
+        ref, _ = o.trace(sph, [320, 200], scene.view_ratio(320, 200), camera.IDENTITY_ROT, [0, 0, 0], rd, 0)
+        with rt.Engine(0, rd) as e:
+            e.set_spheres(sph)
+            e.set_view(320, 200)
+            e.trace(rt.make_push_constants([camera.IDENTITY_ROT], [[0, 0, 0]]))
+            for a, b in zip(e.readback_all_levels(), ref):
+                assert np.array_equal(_bits(a), _bits(b))
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_batch_equals_single_frames(mode, golden, case_table):
+    """16 poses in one rtce_trace_batch == 16 single traces == golden for pose 5 and 15 (1080p)."""
+    meta, _ = golden
+    case = case_table["default_1080p"]
+    rots, poss = camera.bench_camera_path(16)
+    pcs = rt.make_push_constants(rots, poss)
+    with _engine(case, mode, slots=16) as e:
+        e.trace(pcs)
+        batch = [e.readback(-1, k) for k in range(16)]
+        assert oracle.sha256(batch[0]) == meta["default_1080p"]["sha256"][-1]
+        assert oracle.sha256(batch[5]) == meta["default_1080p_pose5"]["sha256"][-1]
+        assert oracle.sha256(batch[15]) == meta["default_1080p_pose15"]["sha256"][-1]
+        lv5 = [e.readback(i, 5) for i in range(e.levels)]
+        assert [oracle.sha256(a) for a in lv5] == meta["default_1080p_pose5"]["sha256"]
+        for k in (3, 9):
+            e.trace(pcs[k:k + 1])
+            assert np.array_equal(_bits(e.readback(-1, 0)), _bits(batch[k]))
+    # fewer slots than frames: chunks reuse slots, last chunk's frames are what remains
+    with _engine(case, mode, slots=4) as e:
+        e.trace(pcs)
+        for k in range(12, 16):
+            assert np.array_equal(_bits(e.readback(-1, k % 4)), _bits(batch[k]))
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_row_band_equals_full_image(mode, case_table):
+    """Multi-GPU invariant: tracing a row band (plus its ancestor rows) gives the full image's bits."""
+    case = case_table["default_800x600"]
+    pcs = rt.make_push_constants([case[6]], [case[7]])
+    with _engine(case, mode) as e:
+        e.trace(pcs)
+        full = e.readback(-1, 0)
+    H, W = full.shape
+    for (x0, y0, x1, y1) in [(0, 0, W, 304), (0, 304, W, 600), (0, 296, W, 312), (40, 48, 200, 120), (0, 592, W, 600)]:
+        with _engine(case, mode) as e:
+            e.set_rect(x0, y0, x1, y1)
+            e.trace(pcs)
+            part = e.readback(-1, 0)
+            assert np.array_equal(_bits(part[y0:y1, x0:x1]), _bits(full[y0:y1, x0:x1])), (x0, y0, x1, y1)
+            assert not part[:y0].any() and not part[y1:].any()
+
+
+def test_render_to_host_and_accumulate(case_table):
+    case = case_table["default_800x600"]
+    rots, poss = camera.bench_camera_path(7)
+    pcs = rt.make_push_constants(rots, poss)
+    with _engine(case, slots=4) as e:
+        singles = []
+        for k in range(7):
+            e.trace(pcs[k:k + 1])
+            singles.append(e.readback(-1, 0))
+        w, h, _ = e.level_info(-1, 0)
+        pin = rt.PinnedBuffer((7, h, w))
+        out = e.render_to_host(pcs, pin.array)
+        for k in range(7):
+            assert np.array_equal(_bits(out[k]), _bits(singles[k])), k
+        out2 = e.render_to_host(pcs)   # pageable destination
+        assert np.array_equal(_bits(out2), _bits(out))
+        pin.free()
+        # accumulation extension: sequential FP32 sum in frame order, then / frames
+        e.trace_accumulate(pcs)
+        acc = e.readback_accum()
+        s = singles[0].copy()
+        for k in range(1, 7):
+            s = (s + singles[k]).astype(np.float32)
+        assert np.array_equal(_bits(acc), _bits((s / np.float32(7)).astype(np.float32)))
+        # static pose: (v + v) / 2 == v exactly
+        st = rt.make_push_constants(*camera.static_path(2))
+        e.trace_accumulate(st)
+        assert np.array_equal(_bits(e.readback_accum()), _bits(singles[0]))
+
+
+def test_large_scene_kernel_matches_checker():
+    """objCount > 8 (CTA-per-ray kernel) on a bigger synthetic scene than the golden cases."""
+    o = oracle.best()
+    sph = scene.synthetic_spheres(3000, seed=0xB200)
+    rot, pos = camera.rotation(0.2, -0.1), np.array([0.5, 0.0, 1.0], np.float32)
+    ref, cnt = o.trace(sph, [96, 56], scene.view_ratio(96, 56), rot, pos, 1000.0, 0)
+    with rt.Engine(0, 1000.0) as e:
+        e.set_option(rt.OPT_COUNTERS, 1)
+        e.set_spheres(sph)
+        e.set_view(96, 56)
+        e.trace(rt.make_push_constants([rot, rot], [pos, pos]))
+        for slot in (0, 1):
+            for i, b in enumerate(ref):
+                assert np.array_equal(_bits(e.readback(i, slot)), _bits(b)), (slot, i)
+        c = e.counters()
+        assert c["R"] == 2 * cnt["R"] and c["E"] == 2 * cnt["E"] and c["S"] == 2 * cnt["S"]
+
+
+def test_error_paths():
+    with rt.Engine(0, 1000.0) as e:
+        with pytest.raises(rt.RtceError):
+            e.trace(rt.make_push_constants([camera.IDENTITY_ROT], [[0, 0, 0]]))   # no scene / view yet
+        with pytest.raises(rt.RtceError):
+            e.set_scene(b"\0" * 100)
+        bad = bytearray(scene.default_mutable_data())
+        bad[4] = 9   # objCount = 9 > MAX_OBJECTS
+        with pytest.raises(rt.RtceError):
+            e.set_scene(bytes(bad))
+        e.set_scene(scene.default_mutable_data())
+        with pytest.raises(rt.RtceError):
+            e.set_view(800, 600, levels=17)
+        e.set_view(800, 600)
+        with pytest.raises(rt.RtceError):
+            e.set_rect(0, 0, 801, 600)
+        with pytest.raises(rt.RtceError):
+            e.readback(7, 0)
