@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 per-level kernels, 2 fused pyramid kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--profile", action="store_true", help="short run for ncu: no e2e, no CPU baseline, no clock hold")
     return ap.parse_args()
 
 
@@ -305,7 +306,7 @@ def run_ours(args, wl):
         ms_total = e0.elapsed_time(e1)
         launches_per_step = eng.counters()["launches"]
         # keep the GPU under the same load long enough for the sampler to see clocks (not timed)
-        t_end = time.perf_counter() + max(0.0, 1.0 - ms_total * 1e-3)
+        t_end = time.perf_counter() + (0.0 if args.profile else max(0.0, 1.0 - ms_total * 1e-3))
         while time.perf_counter() < t_end:
             step()
             torch.cuda.synchronize()
@@ -424,6 +425,8 @@ def main():
     if args.levels:
         wl["levels"] = args.levels
         wl["name"] += f" [levels overridden to {args.levels}]"
+    if args.profile:
+        args.no_e2e = args.no_cpu_baseline = True
     if args.impl == "reference":
         run_reference(args, wl)
         return

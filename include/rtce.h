@@ -158,6 +158,10 @@ int rtce_get_counters(rtce_ctx* ctx, rtce_counters* out);
  * non-contracted FMUL/FADD chains, timed with CUDA events.  Writes lane-operations per second
  * (the denominator of the FP32-issue roofline) and the kernel time in ms. */
 int rtce_measure_fp32_issue(int device, int iters, double* lane_ops_per_s, double* ms);
+/* Exhaustive check (all 2^32 float bit patterns, on the GPU) that the short sqrt / reciprocal
+ * sequences of the hot kernels return the bits of IEEE sqrt.rn / rcp.rn on their stated domains.
+ * out4 = {sqrt mismatches, rcp mismatches, sqrt inputs checked, rcp inputs checked}. */
+int rtce_selftest_math(int device, uint64_t out4[4]);
 
 #ifdef __cplusplus
 }

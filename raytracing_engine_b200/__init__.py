@@ -6,7 +6,7 @@ The product is the C-ABI library `librtce.so` (include/rtce.h); this package is 
 host-side mirror.  Nothing here imports `oracle/` and nothing computes the pass on the CPU.
 """
 from .engine import (Engine, PinnedBuffer, RtceError, PUSH_CONSTANTS_DTYPE, make_push_constants, load_library,
-                     host_level_count, host_level_dims, host_image_size, LIB_PATH, measure_fp32_issue,
+                     host_level_count, host_level_dims, host_image_size, LIB_PATH, measure_fp32_issue, selftest_math,
                      OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED)
 from . import scene, camera
 

@@ -56,6 +56,42 @@ struct LevelParamsLarge {
 };
 cudaError_t launch_trace_level_large(const LevelParamsLarge& p, int frames, bool count, cudaStream_t st);
 
+// ---- fused pyramid kernel (objCount <= 8): ALL levels of a frame batch in ONE launch ---------
+// One CTA owns one 64x64 tile of the final level and, before it, the tile's ancestor regions on
+// every coarser level (32x32, 16x16, ... 1 pixel), handing each level to the next through shared
+// memory.  Legal because a pixel's value is a pure function of (x, y, level, uniforms): ancestors
+// shared by several tiles are recomputed per tile with identical bits.
+constexpr int kFusedTile = 64;
+constexpr int kFusedThreads = 256;
+constexpr int kFusedMaxSide = 72;      // largest region side at any level (table size)
+constexpr int kFusedOddPitch = 44;     // parent buffer of shift 1, 3, 5, ... (region side <= 44)
+constexpr int kFusedEvenPitch = 28;    // parent buffer of shift 2, 4, 6, ... (region side <= 28)
+
+struct FusedLevel {
+    unsigned long long off;   // float offset of the level image inside a frame slot
+    float isx, isy;           // pc.imageSize at this level (main.rs:303-305)
+    float threshold;          // compute.glsl:75
+    int w, h;                 // level image size (pitch = w)
+    int rx0, ry0, rx1, ry1;   // region of interest at this level (whole level, or a rect's ancestors)
+};
+
+struct FusedParams {
+    float* base;              // frame slot 0 of the pyramid
+    size_t slot_stride;
+    unsigned long long* counters;
+    int levels, n_spheres;
+    int gx0, gy0;             // final-level origin of the tile grid (multiple of kFusedTile)
+    int ntx, nty;
+    float ratx, raty, render_dist;
+    FusedLevel lv[kMaxLevels];
+    float4 sph[kSmallSceneMax];
+    Cam cam[kMaxBatch];
+};
+// Returns cudaErrorNotSupported when the geometry does not fit the kernel's shared-memory regions
+// (the caller then uses the per-level kernels).
+bool fused_geometry_ok(const FusedParams& p);
+cudaError_t launch_trace_fused(const FusedParams& p, int frames, bool count, cudaStream_t st);
+
 // Accumulation extension: acc = (first ? 0 : acc) + img ; and the final scale by 1/frames.
 cudaError_t launch_accumulate(float* acc, const float* img, size_t n, bool first, cudaStream_t st);
 cudaError_t launch_scale(float* acc, size_t n, float divisor, cudaStream_t st);

@@ -65,3 +65,62 @@ extern "C" int rtce_measure_fp32_issue(int device, int iters, double* lane_ops_p
     cudaSetDevice(prev);
     return rc;
 }
+
+// ------------------------------------------------------------------------------------------------
+// rtce_selftest_math — exhaustive proof-by-enumeration that rtce::sqrt_fast / rtce::rcp_fast return
+// the bits of sqrt.rn / rcp.rn on their stated domains (all 2^32 float bit patterns are visited).
+// ------------------------------------------------------------------------------------------------
+#include "rtce_device.cuh"
+
+namespace {
+
+__global__ void __launch_bounds__(256) k_selftest_math(unsigned long long* out /* [4] */) {
+    unsigned long long bad_sqrt = 0, bad_rcp = 0, n_sqrt = 0, n_rcp = 0;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long b = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; b < (1ull << 32); b += stride) {
+        const float x = __uint_as_float((unsigned)b);
+        const float ax = fabsf(x);
+        // sqrt domain: +0 and finite x >= 2^-101 (bit pattern 0x0d000000)
+        if (b == 0ull || (b >= 0x0d000000ull && b < 0x7f800000ull)) {
+            n_sqrt++;
+            if (__float_as_uint(rtce::sqrt_fast(x)) != __float_as_uint(__fsqrt_rn(x))) bad_sqrt++;
+        }
+        // rcp domain: 2^-126 <= |x| <= 2^126
+        if (ax >= 1.17549435e-38f && ax <= 8.50705917e37f) {
+            n_rcp++;
+            if (__float_as_uint(rtce::rcp_fast(x)) != __float_as_uint(__frcp_rn(x))) bad_rcp++;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        bad_sqrt += __shfl_down_sync(0xffffffffu, bad_sqrt, o);
+        bad_rcp += __shfl_down_sync(0xffffffffu, bad_rcp, o);
+        n_sqrt += __shfl_down_sync(0xffffffffu, n_sqrt, o);
+        n_rcp += __shfl_down_sync(0xffffffffu, n_rcp, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(out + 0, bad_sqrt);
+        atomicAdd(out + 1, bad_rcp);
+        atomicAdd(out + 2, n_sqrt);
+        atomicAdd(out + 3, n_rcp);
+    }
+}
+
+}  // namespace
+
+extern "C" int rtce_selftest_math(int device, uint64_t out4[4]) {
+    if (!out4) return RTCE_ERR_INVALID;
+    int prev = 0;
+    if (cudaGetDevice(&prev) != cudaSuccess) return RTCE_ERR_CUDA;
+    if (cudaSetDevice(device) != cudaSuccess) return RTCE_ERR_CUDA;
+    unsigned long long* d = nullptr;
+    int rc = RTCE_OK;
+    if (cudaMalloc(&d, 32) != cudaSuccess) return RTCE_ERR_CUDA;
+    cudaMemset(d, 0, 32);
+    k_selftest_math<<<148 * 8, 256>>>(d);
+    unsigned long long h[4] = {0, 0, 0, 0};
+    if (cudaMemcpy(h, d, 32, cudaMemcpyDeviceToHost) != cudaSuccess) rc = RTCE_ERR_CUDA;
+    for (int i = 0; i < 4; i++) out4[i] = h[i];
+    cudaFree(d);
+    cudaSetDevice(prev);
+    return rc;
+}

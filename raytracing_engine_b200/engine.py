@@ -32,7 +32,7 @@ EXPORTS = [
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
     "rtce_trace_accumulate", "rtce_accum_info", "rtce_readback", "rtce_readback_accum",
     "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_get_counters",
-    "rtce_measure_fp32_issue",
+    "rtce_measure_fp32_issue", "rtce_selftest_math",
 ]
 
 
@@ -87,6 +87,7 @@ def load_library() -> C.CDLL:
         "rtce_sync": (i32, [vp]),
         "rtce_get_counters": (i32, [vp, C.POINTER(_Counters)]),
         "rtce_measure_fp32_issue": (i32, [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+        "rtce_selftest_math": (i32, [i32, C.POINTER(C.c_uint64)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -130,6 +131,16 @@ def measure_fp32_issue(device: int = 0, iters: int = 4096):
     if r != RTCE_OK:
         raise RtceError(f"rtce_measure_fp32_issue: {r}")
     return ops.value, ms.value
+
+
+def selftest_math(device: int = 0) -> dict:
+    """Exhaustive GPU check of the short sqrt / rcp sequences against sqrt.rn / rcp.rn."""
+    out = (C.c_uint64 * 4)()
+    r = load_library().rtce_selftest_math(int(device), out)
+    if r != RTCE_OK:
+        raise RtceError(f"rtce_selftest_math: {r}")
+    return {"sqrt_mismatches": int(out[0]), "rcp_mismatches": int(out[1]),
+            "sqrt_checked": int(out[2]), "rcp_checked": int(out[3])}
 
 
 def make_push_constants(rots, poss) -> np.ndarray:

@@ -210,3 +210,11 @@ def test_error_paths():
             e.set_rect(0, 0, 801, 600)
         with pytest.raises(rt.RtceError):
             e.readback(7, 0)
+
+
+def test_fast_math_is_correctly_rounded_exhaustively():
+    """All 2^32 float bit patterns: the kernels' short sqrt / rcp sequences == sqrt.rn / rcp.rn on their domains."""
+    r = rt.selftest_math(0)
+    assert r["sqrt_mismatches"] == 0 and r["rcp_mismatches"] == 0, r
+    assert r["sqrt_checked"] == 1 + (0x7F800000 - 0x0D000000)          # +0 and every finite x >= 2^-101
+    assert r["rcp_checked"] == 2 * (0x7E800000 - 0x00800000 + 1)       # 2^-126 <= |x| <= 2^126
