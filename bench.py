@@ -47,7 +47,9 @@ def parse_args():
     ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS))
     ap.add_argument("--frames", type=int, default=None, help="override frames per step (labelled in config)")
     ap.add_argument("--levels", type=int, default=None, help="override pyramid levels (configs[3] sweep)")
-    ap.add_argument("--kernel", type=int, default=0, help="0 auto, 1 per-level kernels, 2 fused pyramid kernel")
+    ap.add_argument("--kernel", type=int, default=0, help="0 auto (= 3), 1 per-pixel kernel per level, 2 fused pyramid kernel, 3 strip kernels + fused coarse levels")
+    ap.add_argument("--strip-min-rays", type=int, default=None, help="kernel plan 3: strip-kernel threshold (rays per launch)")
+    ap.add_argument("--groups", type=int, default=None, help="kernel plan 3: frame groups per batch (1 or 2)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--profile", action="store_true", help="short run for ncu: no e2e, no CPU baseline, no clock hold")
@@ -227,6 +229,10 @@ def run_ours(args, wl):
     stream = torch.cuda.Stream(device=local_rank)
     eng.set_stream(stream.cuda_stream)
     eng.set_option(rt.OPT_KERNEL, args.kernel)
+    if args.strip_min_rays is not None:
+        eng.set_option(rt.OPT_STRIP_MIN_RAYS, args.strip_min_rays)
+    if args.groups is not None:
+        eng.set_option(rt.OPT_GROUPS, args.groups)
     slots = min(frames, 16)
     eng.set_option(rt.OPT_FRAME_SLOTS, slots)
     if len(spheres) <= 8:
@@ -406,7 +412,7 @@ def run_ours(args, wl):
                    "ms_per_frame": ms_step / frames,
                    "parallelism": "1 GPU" if n_gpus == 1 else f"{n_gpus} row bands of the final level + one NCCL gather to rank 0 per step",
                    "l2": f"no flush: each step rewrites {bytes_step / 1e6:.0f} MB of pyramid (> 126 MB L2 when frames >= 12 at 1080p); parents are meant to be L2 hits",
-                   "kernel": {0: "auto", 1: "per-level", 2: "fused"}[args.kernel]},
+                   "kernel": {0: "auto (strip + fused coarse levels)", 1: "per-level", 2: "fused", 3: "strip + fused coarse levels"}[args.kernel]},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps),
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "mprimary_per_s": Wf * Hf * frames / (ms_step * 1e-3) / 1e6,

@@ -90,7 +90,12 @@ typedef struct rtce_counters {
 typedef enum rtce_option {
     RTCE_OPT_COUNTERS = 1,      /* 0/1: count R/E/S on the device (slower kernels; off by default) */
     RTCE_OPT_FRAME_SLOTS = 2,   /* frames traced concurrently by rtce_trace_batch (pyramid replicas), default 16 */
-    RTCE_OPT_KERNEL = 3         /* 0 = auto, 1 = per-level kernels, 2 = fused-pyramid kernel */
+    RTCE_OPT_KERNEL = 3,        /* 0 = auto (= 3), 1 = per-pixel kernel per level, 2 = fused-pyramid kernel,
+                                   3 = strip kernel per large level + fused-pyramid kernel for the coarse levels */
+    RTCE_OPT_STRIP_MIN_RAYS = 4,/* kernel plan 3: a level is traced by the strip kernel when it has at least this
+                                   many rays per launch (level pixels x frames of the launch), default 400000 */
+    RTCE_OPT_GROUPS = 5         /* kernel plan 3: 1 = one launch chain per batch, 2 (default) = the batch's frames in
+                                   two groups on two streams so that latency-bound launches overlap issue-bound ones */
 } rtce_option;
 
 /* -- lifetime ------------------------------------------------------------------------------
@@ -162,6 +167,15 @@ int rtce_measure_fp32_issue(int device, int iters, double* lane_ops_per_s, doubl
  * sequences of the hot kernels return the bits of IEEE sqrt.rn / rcp.rn on their stated domains.
  * out4 = {sqrt mismatches, rcp mismatches, sqrt inputs checked, rcp inputs checked}. */
 int rtce_selftest_math(int device, uint64_t out4[4]);
+
+/* Diagnostics: warp timeline of the strip-kernel launch that traces `level` (negative = from the last
+ * level).  First call arms it; a later call copies 4 words per warp {start ns, tickets exhausted ns,
+ * exit ns, tasks taken} of the most recent launch into `out` and re-arms.  max_warps = 0 disarms. */
+int rtce_debug_strip_timeline(rtce_ctx* ctx, int level, uint64_t* out, int max_warps);
+/* Diagnostics: launch timeline.  out == NULL arms it (an event pair around every kernel launch from now
+ * on); a later call writes 6 doubles per launch {start ms, end ms, kind (1 strip, 2 overflow, 10 fused),
+ * level, frame group, 0} and returns how many; it stays armed while max_launches > 0.  Synchronises. */
+int rtce_debug_launch_timeline(rtce_ctx* ctx, double* out, int max_launches);
 
 #ifdef __cplusplus
 }

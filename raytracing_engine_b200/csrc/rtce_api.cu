@@ -16,12 +16,21 @@
 
 using namespace rtce;
 
+static constexpr unsigned kOverflowCap = 1u << 19;   // rays per frame group; 2 x 38 MB
+
 struct rtce_ctx {
     int device = 0;
     float render_dist = 1000.0f;
     cudaStream_t own_stream = nullptr;   // created by rtce_create
     cudaStream_t stream = nullptr;       // the stream work is issued on (own_stream or the caller's)
     cudaStream_t copy_stream = nullptr;  // D2H copies of rtce_render_to_host
+    cudaStream_t aux_stream = nullptr;   // second frame group of a chunk (lower priority; forked from / joined to `stream`)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int groups = 2;                      // RTCE_OPT_GROUPS
+    // diagnostics (rtce_debug_launch_timeline): an event pair around every kernel launch
+    struct LaunchMark { cudaEvent_t e0, e1; int kind, level, group; };
+    bool mark_launches = false;
+    std::vector<LaunchMark> marks;
     cudaEvent_t ev_traced[2] = {nullptr, nullptr};
     cudaEvent_t ev_copied[2] = {nullptr, nullptr};
     std::string err;
@@ -51,7 +60,12 @@ struct rtce_ctx {
     // options / counters
     bool count = false;
     int kernel_mode = 0;
+    long long strip_min_rays = 400000;   // a level goes to the strip kernel when it has this many rays per launch
     unsigned long long* d_counters = nullptr;
+    unsigned long long* d_dbg = nullptr;   // strip-kernel warp timeline of one level (rtce_debug_strip_timeline)
+    int dbg_level = -1;
+    int* d_tickets = nullptr;    // [kMaxLevels][4] {task ticket, overflow count, overflow head, -} of the strip launches, zeroed per chunk
+    float* d_oq = nullptr;       // overflow queue of the strip launches (kOverflowCap rays x 18 words), reused level after level
     uint64_t launches = 0;
 };
 
@@ -136,9 +150,16 @@ int rtce_create(int device, float render_dist, rtce_ctx** out) {
     c->device = device;
     c->render_dist = render_dist;
     DeviceGuard g(device);
-    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);   // lo = numerically greatest = least urgent
+    if (cudaStreamCreateWithPriority(&c->own_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&c->aux_stream, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long)) != cudaSuccess) {
+        cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMalloc(&c->d_tickets, sizeof(int) * 2 * kMaxLevels * 4) != cudaSuccess ||
+        cudaMalloc(&c->d_oq, sizeof(float) * 2 * (size_t)kOverflowCap * (10 + kSmallSceneMax)) != cudaSuccess) {
         rtce_destroy(c);
         return RTCE_ERR_CUDA;
     }
@@ -156,6 +177,9 @@ void rtce_destroy(rtce_ctx* c) {
     DeviceGuard g(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+    if (c->aux_stream) cudaStreamSynchronize(c->aux_stream);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     for (int i = 0; i < 2; i++) {
         if (c->ev_traced[i]) cudaEventDestroy(c->ev_traced[i]);
         if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
@@ -164,8 +188,12 @@ void rtce_destroy(rtce_ctx* c) {
     if (c->d_accum) cudaFree(c->d_accum);
     if (c->d_spheres) cudaFree(c->d_spheres);
     if (c->d_counters) cudaFree(c->d_counters);
+    if (c->d_tickets) cudaFree(c->d_tickets);
+    if (c->d_oq) cudaFree(c->d_oq);
+    if (c->d_dbg) cudaFree(c->d_dbg);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
+    if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
     delete c;
 }
 
@@ -182,8 +210,16 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             }
             return RTCE_OK;
         case RTCE_OPT_KERNEL:
-            if (value < 0 || value > 2) return fail(c, RTCE_ERR_INVALID, "kernel mode out of range");
+            if (value < 0 || value > 3) return fail(c, RTCE_ERR_INVALID, "kernel mode out of range");
             c->kernel_mode = (int)value;
+            return RTCE_OK;
+        case RTCE_OPT_GROUPS:
+            if (value < 1 || value > 2) return fail(c, RTCE_ERR_INVALID, "groups out of range");
+            c->groups = (int)value;
+            return RTCE_OK;
+        case RTCE_OPT_STRIP_MIN_RAYS:
+            if (value < 0) return fail(c, RTCE_ERR_INVALID, "strip threshold out of range");
+            c->strip_min_rays = (long long)value;
             return RTCE_OK;
         default: return fail(c, RTCE_ERR_INVALID, "unknown option");
     }

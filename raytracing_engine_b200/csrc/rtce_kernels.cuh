@@ -92,6 +92,54 @@ struct FusedParams {
 bool fused_geometry_ok(const FusedParams& p);
 cudaError_t launch_trace_fused(const FusedParams& p, int frames, bool count, cudaStream_t st);
 
+// ---- strip kernel (objCount <= 8): ONE level of a frame batch, persistent warps ---------------
+// The levels that hold almost all rays (the last three: 75 % + 19 % + 5 %) are each traced by one
+// launch of persistent, barrier-free warps.  A warp task is a 32-wide x `rows`-high tile of the
+// level; a lane keeps one image column for the whole task.  Rays that need more than two march
+// trips are parked in a per-warp shared-memory queue that persists across the warp's tasks and
+// is marched with lane refill (DESIGN.md "Strip kernel").
+constexpr int kStripThreads = 256;
+constexpr int kStripMaxRows = 32;      // rows per task (row-term table size)
+
+struct StripParams {
+    float* out;               // level image of frame slot 0
+    const float* parent;      // level-1 image of frame slot 0; nullptr at level 0 (start = 1.0)
+    size_t slot_stride;       // floats between frame slots (frames * slot_stride < 2^32: queue offsets are 32-bit)
+    unsigned long long* counters;
+    int* tickets;             // zero-initialised task counter of this launch
+    float* oq;                // overflow queue: rays that outlive kMaxAge trips in a warp's tail go here (nullptr = none)
+    unsigned* oq_count;       // zero-initialised number of rays in oq
+    unsigned oq_cap;          // capacity of oq in rays; word w of ray k is oq[w * oq_cap + k]
+    unsigned long long* dbg;  // nullptr, or 4 words per warp: globaltimer at start / tickets exhausted / exit, tasks done
+    int w, pw;                // row pitch of this level and of the parent level
+    int x0, y0, x1, y1;       // region of interest at this level
+    int ntx, nty;             // tasks per frame: 32-wide columns x `rows`-high rows covering the ROI
+    int rows;                 // rows per task, 1..kStripMaxRows
+    int frames;
+    int n_spheres;
+    float isx, isy, ratx, raty, threshold, render_dist;
+    float4 sph[kSmallSceneMax];
+    Cam cam[kMaxBatch];
+};
+cudaError_t launch_trace_strip(const StripParams& p, bool count, cudaStream_t st);
+
+// Second half of a strip launch: marches the rays of its overflow queue to the end.  The long rays
+// (cones grazing a sphere: 10 .. 100+ march trips, 0.2 % of all rays but a quarter of all trips,
+// clustered in a few tiles) would otherwise serialise in the warp that found them; here every warp
+// of the device draws them 32 at a time, with lane refill.
+struct OverflowParams {
+    float* out;                 // level image of frame slot 0 (queue entries carry offsets from here)
+    const float* oq;
+    const unsigned* oq_count;
+    unsigned* oq_head;          // zero-initialised consumer cursor
+    unsigned oq_cap;
+    unsigned long long* counters;
+    int n_spheres;
+    float threshold, render_dist;
+    float4 sph[kSmallSceneMax];
+};
+cudaError_t launch_march_overflow(const OverflowParams& p, bool count, cudaStream_t st);
+
 // Accumulation extension: acc = (first ? 0 : acc) + img ; and the final scale by 1/frames.
 cudaError_t launch_accumulate(float* acc, const float* img, size_t n, bool first, cudaStream_t st);
 cudaError_t launch_scale(float* acc, size_t n, float divisor, cudaStream_t st);

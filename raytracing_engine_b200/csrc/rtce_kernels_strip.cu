@@ -1,0 +1,491 @@
+// rtce_kernels_strip.cu — ONE pyramid level of a frame batch per launch, objCount <= 8, traced by
+// persistent barrier-free warps (DESIGN.md "Strip kernel").  This is the dispatch of
+// src/main.rs:314 for the levels that hold almost all rays.
+//
+// Work decomposition
+//   grid = one resident wave of CTAs; warps draw tasks (frame, tile) from one atomic ticket counter.
+//   A task is a 32-wide x `rows`-high tile of the level: lane = image column for the whole
+//   task, so the column terms of the ray direction live in registers; the row terms of the task's
+//   rows are computed once (lane r computes row r) into a per-warp shared-memory table and read back
+//   as one broadcast LDS.128 per row.  Stores are full 128-byte rows.
+//
+// Divergence (measured on the default scene, all levels >= 2: 77 % of rays end in the first march
+// trip, 20 % in the second, 3 % form a long tail of up to ~30 trips; hit pixels are spatially
+// coherent, the tail is not):
+//   trip 1  is straight-line code for all 32 lanes (no SDF evaluation: see first_step);
+//   trip 2  runs in place, under one warp-uniform branch (taken by the ~23 % of warps that cover
+//           hit pixels, where nearly all lanes take it);
+//   trips 3.. are rare per warp, so those rays are compacted: ballot + prefix-popcount push into a
+//           per-warp shared-memory queue that PERSISTS across the warp's tasks, and are marched 32
+//           at a time with lane refill (a finished lane pops the next queued ray as soon as
+//           kRefillMin lanes are free), so the tail runs at >= 50 % lane occupancy instead of the
+//           ~20 % of lock-step marching.  Nothing waits on a parked ray: the level's children are
+//           traced by the next launch.
+#include "rtce_march.cuh"
+
+namespace rtce {
+
+constexpr int kQCap = 64;          // queue entries per warp: < 32 parked + <= 32 pushed by one row
+constexpr int kRefillMin = 8;      // refill when this many lanes are idle
+constexpr int kPinWords = 40;       // per-warp scratch for pinning uniforms (>= 2 + 4 * 8, multiple of 4)
+constexpr int kMaxAge = 6;         // tail trips after which a ray is evicted to the overflow queue
+constexpr int kEvictMin = 8;       // evict in groups of at least this many rays (or when the local queue is empty)
+constexpr int kLeaveBelow = 16;    // with the queue empty, park the stragglers below this many active lanes
+#define RTCE_SQ_WORDS(N) (10 + (N))   // o(3) s(3) len last start offset d[N]
+#define RTCE_FULL 0xffffffffu
+
+template <int N>
+RTCE_DEV void sq_push(float* q, int idx, const Ray<N>& r, float len, float last, float start, unsigned off) {
+    q[0 * kQCap + idx] = r.ox;
+    q[1 * kQCap + idx] = r.oy;
+    q[2 * kQCap + idx] = r.oz;
+    q[3 * kQCap + idx] = r.sx;
+    q[4 * kQCap + idx] = r.sy;
+    q[5 * kQCap + idx] = r.sz;
+    q[6 * kQCap + idx] = len;
+    q[7 * kQCap + idx] = last;
+    q[8 * kQCap + idx] = start;
+    q[9 * kQCap + idx] = __uint_as_float(off);
+#pragma unroll
+    for (int i = 0; i < N; i++) q[(10 + i) * kQCap + idx] = r.d[i];
+}
+
+template <int N>
+RTCE_DEV void sq_pop(const float* q, int idx, Ray<N>& r, float& len, float& last, float& start, unsigned& off) {
+    r.ox = q[0 * kQCap + idx];
+    r.oy = q[1 * kQCap + idx];
+    r.oz = q[2 * kQCap + idx];
+    r.sx = q[3 * kQCap + idx];
+    r.sy = q[4 * kQCap + idx];
+    r.sz = q[5 * kQCap + idx];
+    len = q[6 * kQCap + idx];
+    last = q[7 * kQCap + idx];
+    start = q[8 * kQCap + idx];
+    off = __float_as_uint(q[9 * kQCap + idx]);
+#pragma unroll
+    for (int i = 0; i < N; i++) r.d[i] = q[(10 + i) * kQCap + idx];
+}
+
+// Overflow queue in global memory (structure of arrays, word w of ray k at oq[w * cap + k]).
+struct OverflowQueue {
+    float* buf;
+    unsigned* count;
+    unsigned cap;
+};
+
+template <int N>
+RTCE_DEV void oq_store(const OverflowQueue& oq, unsigned k, const Ray<N>& r, float len, float last, float start, unsigned off) {
+    float* b = oq.buf + k;
+    const size_t c = oq.cap;
+    b[0 * c] = r.ox; b[1 * c] = r.oy; b[2 * c] = r.oz;
+    b[3 * c] = r.sx; b[4 * c] = r.sy; b[5 * c] = r.sz;
+    b[6 * c] = len; b[7 * c] = last; b[8 * c] = start;
+    b[9 * c] = __uint_as_float(off);
+#pragma unroll
+    for (int i = 0; i < N; i++) b[(10 + i) * c] = r.d[i];
+}
+
+template <int N>
+RTCE_DEV void oq_load(const float* buf, unsigned cap, unsigned k, Ray<N>& r, float& len, float& last, float& start, unsigned& off) {
+    const float* b = buf + k;
+    const size_t c = cap;
+    r.ox = __ldcg(b + 0 * c); r.oy = __ldcg(b + 1 * c); r.oz = __ldcg(b + 2 * c);
+    r.sx = __ldcg(b + 3 * c); r.sy = __ldcg(b + 4 * c); r.sz = __ldcg(b + 5 * c);
+    len = __ldcg(b + 6 * c); last = __ldcg(b + 7 * c); start = __ldcg(b + 8 * c);
+    off = __float_as_uint(__ldcg(b + 9 * c));
+#pragma unroll
+    for (int i = 0; i < N; i++) r.d[i] = __ldcg(b + (10 + i) * c);
+}
+
+// March queued rays (trips 3.. of compute.glsl:44-66) with lane refill.  drain = false: called with
+// a full warp's worth queued; returns once the queue is empty and fewer than kLeaveBelow lanes are
+// still marching, parking those back in the queue.  drain = true: runs until every ray is finished
+// or evicted.  A ray that has marched kMaxAge trips in here is a long one (a cone grazing a sphere:
+// 10 .. 100+ trips): it is evicted to the global overflow queue, which the whole device marches
+// after this kernel (k_march_overflow), instead of serialising in this warp.
+template <int N, bool COUNT>
+RTCE_DEV int tail_march(float* q, int qn, const bool drain, float* __restrict__ img, const float thr, const float rd,
+                        const float4* __restrict__ sph, const OverflowQueue& oq, bool& oq_open, unsigned& cE, unsigned& cS,
+                        const int lane) {
+    const unsigned lt = (1u << lane) - 1u;
+    bool active = false;
+    Ray<N> r;
+    float len = 0.0f, last = 0.0f, start = 0.0f;
+    unsigned off = 0;
+    int age = 0;
+    for (;;) {
+        unsigned am = __ballot_sync(RTCE_FULL, active);
+        if (oq_open) {
+            const bool old = active && age >= kMaxAge;
+            const unsigned om = __ballot_sync(RTCE_FULL, old);
+            if (om != 0u && (__popc(om) >= kEvictMin || qn == 0)) {
+                const int n = __popc(om);
+                unsigned base = 0;
+                if (lane == __ffs(om) - 1) base = atomicAdd(oq.count, (unsigned)n);
+                base = __shfl_sync(RTCE_FULL, base, __ffs(om) - 1);
+                const unsigned k = base + (unsigned)__popc(om & lt);
+                if (old && k < oq.cap) {   // every slot below min(count, cap) is written: the consumer reads exactly those
+                    oq_store<N>(oq, k, r, len, last, start, off);
+                    active = false;
+                }
+                if (base + (unsigned)n > oq.cap) oq_open = false;   // full: the rest is marched here
+                am = __ballot_sync(RTCE_FULL, active);
+            }
+        }
+        const int nact = __popc(am);
+        if (qn > 0 && 32 - nact >= kRefillMin) {
+            const int rank = __popc(~am & lt);
+            if (!active && rank < qn) {
+                sq_pop<N>(q, qn - 1 - rank, r, len, last, start, off);
+                active = true;
+                age = 0;
+            }
+            qn -= min(32 - nact, qn);
+            __syncwarp();
+        } else if (am == 0u) {
+            break;
+        } else if (!drain && qn == 0 && nact < kLeaveBelow) {
+            if (active) sq_push<N>(q, __popc(am & lt), r, len, last, start, off);
+            qn = nact;
+            __syncwarp();
+            break;
+        }
+        if (active) {
+            unsigned e = 0, s = 0;
+            const bool go = march_step<N, COUNT>(r, len, last, thr, rd, sph, e, s);
+            if (COUNT) { cE += e; cS += s; }
+            age++;
+            if (!go) {
+                img[off] = glsl_max(fadd(start, len), 0.0f);   // compute.glsl:84, :86
+                active = false;
+            }
+        }
+    }
+    return qn;
+}
+
+// The overflow queue of one strip launch, marched to the end by every warp of the device.
+template <int N, bool COUNT>
+__global__ void __launch_bounds__(256)
+    k_march_overflow(const __grid_constant__ OverflowParams P) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    const unsigned n = min(*P.oq_count, P.oq_cap);
+    if (n == 0u) return;
+    float4 sph[N > 0 ? N : 1];
+#pragma unroll
+    for (int i = 0; i < N; i++) sph[i] = P.sph[i];
+    const float thr = P.threshold, rd = P.render_dist;
+    float* const img = P.out;
+    unsigned cE = 0, cS = 0;
+    bool active = false, exhausted = false;
+    Ray<N> r;
+    float len = 0.0f, last = 0.0f, start = 0.0f;
+    unsigned off = 0;
+    for (;;) {
+        const unsigned am = __ballot_sync(RTCE_FULL, active);
+        const int nfree = 32 - __popc(am);
+        if (!exhausted && nfree >= kRefillMin) {
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(P.oq_head, (unsigned)nfree);
+            base = __shfl_sync(RTCE_FULL, base, 0);
+            const unsigned k = base + (unsigned)__popc(~am & lt);
+            if (!active && k < n) {
+                oq_load<N>(P.oq, P.oq_cap, k, r, len, last, start, off);
+                active = true;
+            }
+            if (base + (unsigned)nfree >= n) exhausted = true;
+        } else if (am == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        if (active) {
+            unsigned e = 0, s = 0;
+            const bool go = march_step<N, COUNT>(r, len, last, thr, rd, sph, e, s);
+            if (COUNT) { cE += e; cS += s; }
+            if (!go) {
+                img[off] = glsl_max(fadd(start, len), 0.0f);   // compute.glsl:84, :86
+                active = false;
+            }
+        }
+    }
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) {
+            cE += __shfl_down_sync(RTCE_FULL, cE, o);
+            cS += __shfl_down_sync(RTCE_FULL, cS, o);
+        }
+        if (lane == 0) {
+            atomicAdd(P.counters + 1, (unsigned long long)cE);
+            atomicAdd(P.counters + 2, (unsigned long long)cS);
+        }
+    }
+}
+
+// First trip of the march loop for RENDER_DIST > 0, branch-free (see first_step in rtce_march.cuh).
+template <int N, bool COUNT>
+RTCE_DEV bool first_trip(const Ray<N>& r, float& len, const float thr, const float rd, unsigned& cE, unsigned& cS) {
+    float dist = rd;   // compute.glsl:49
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        if (COUNT) cE += (r.d[i] <= thr) ? 1u : 0u;
+        dist = glsl_min(dist, r.d[i]);
+    }
+    if (COUNT) {
+        cE += N;
+        cS++;
+    }
+    const float last = glsl_max(dist, 0.0f);   // :59; len = 0 + last
+    const bool hit = dist <= thr;              // :62 (radius = (0 + 1) * threshold)
+    len = hit ? fsub(last, thr) : last;        // :63
+    return !hit && last < rd;                  // :44
+}
+
+RTCE_DEV unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+#ifndef RTCE_STRIP_MIN_BLOCKS
+#define RTCE_STRIP_MIN_BLOCKS 3
+#endif
+
+template <int N, bool COUNT, bool HAS_PARENT>
+__global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
+    k_trace_strip(const __grid_constant__ StripParams P) {
+    extern __shared__ __align__(16) float s_mem[];
+    constexpr int kWarpWords = RTCE_SQ_WORDS(N) * kQCap + 4 * kStripMaxRows + kPinWords;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float* const q = s_mem + warp * kWarpWords;
+    float4* const rowtab = reinterpret_cast<float4*>(q + RTCE_SQ_WORDS(N) * kQCap);
+
+    // Loop-invariant uniforms are PINNED in registers: ptxas re-materialises plain parameter loads
+    // inside the row loop (13 LDC/LDCU per row = 10 % of its issue slots; it also sees through a
+    // shuffle of a uniform value).  A value read back through a volatile shared-memory load cannot
+    // be re-materialised.  Scene and level constants once per warp, the camera once per task.
+    volatile float* const pin = reinterpret_cast<volatile float*>(rowtab + kStripMaxRows);   // kPinWords floats
+    float4 sph[N > 0 ? N : 1];
+    float thr, rd;
+    {
+        pin[0] = P.threshold;
+        pin[1] = P.render_dist;
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            pin[2 + 4 * i + 0] = P.sph[i].x;
+            pin[2 + 4 * i + 1] = P.sph[i].y;
+            pin[2 + 4 * i + 2] = P.sph[i].z;
+            pin[2 + 4 * i + 3] = P.sph[i].w;
+        }
+        __syncwarp();
+        thr = pin[0];
+        rd = pin[1];
+#pragma unroll
+        for (int i = 0; i < N; i++) sph[i] = make_float4(pin[2 + 4 * i + 0], pin[2 + 4 * i + 1], pin[2 + 4 * i + 2], pin[2 + 4 * i + 3]);
+        __syncwarp();
+    }
+    float* const img = P.out;   // frame slot 0; queue entries carry offsets from here
+    const OverflowQueue oq{P.oq, P.oq_count, P.oq_cap};
+    bool oq_open = P.oq != nullptr;   // warp-uniform
+    const int tiles = P.ntx * P.nty;
+    const int tasks = tiles * P.frames;
+    const int nwarps = gridDim.x * (kStripThreads / 32);
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned cR = 0, cE = 0, cS = 0;
+    int qn = 0;   // warp-uniform
+
+    // Tasks (frame-major) are handed out dynamically, one atomic per task fetched one task ahead:
+    // march cost differs by > 2x between tiles that cover spheres and tiles that see only
+    // background, and between the frames of a batch.
+    int task = blockIdx.x * (kStripThreads / 32) + warp;   // the first round is static
+    int next = 0;
+    unsigned long long t0 = 0, t1 = 0;
+    int ndone = 0;
+    if (P.dbg) t0 = globaltimer_ns();
+    while (task < tasks) {
+        ndone++;
+        if (lane == 0) next = atomicAdd(P.tickets, 1) + nwarps;
+        const int f = task / tiles, tile = task - f * tiles;
+        const int ty = tile / P.ntx, tx = tile - ty * P.ntx;
+        Cam cam;
+        {
+            const Cam& c0 = P.cam[f];
+#pragma unroll
+            for (int i = 0; i < 4; i++) pin[i] = c0.rot[i];
+#pragma unroll
+            for (int i = 0; i < 3; i++) pin[4 + i] = c0.pos[i];
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; i++) cam.rot[i] = pin[i];
+#pragma unroll
+            for (int i = 0; i < 3; i++) cam.pos[i] = pin[4 + i];
+            cam.pad = 0.0f;
+        }
+        const int x = P.x0 + tx * 32 + lane;
+        const bool xok = x < P.x1;
+        const int xc = min(x, P.x1 - 1);   // lanes past the region repeat its last column and store nothing
+        const int yb = P.y0 + ty * P.rows;
+        const int rows = min(P.rows, P.y1 - yb);
+        const float4 col = col_terms(cam, norm_coord(xc, P.isx, P.ratx));
+        __syncwarp();   // the previous task's table reads are done
+        if (lane < rows) rowtab[lane] = row_terms(cam, norm_coord(yb + lane, P.isy, P.raty));
+        __syncwarp();
+        float* op = img + ((size_t)f * P.slot_stride + (size_t)yb * P.w + xc);   // this lane's texel, row by row
+        // :80-82  rows 2k and 2k+1 share the parent texel; it is fetched one row pair ahead
+        const float* pp = nullptr;
+        float start = 1.0f, ahead = 0.0f;   // compute.glsl:79
+        int pairs_left = 0;                 // parent rows still to fetch after `ahead`
+        if (HAS_PARENT) {
+            pp = P.parent + ((size_t)f * P.slot_stride + (size_t)(yb >> 1) * P.pw + (xc >> 1));
+            pairs_left = ((yb + rows - 1) >> 1) - (yb >> 1);
+            start = __ldg(pp);
+            if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
+        }
+        for (int rr = 0; rr < rows; rr++, op += P.w) {
+            const float4 row = rowtab[rr];
+            Ray<N> ray;
+            ray_setup<N>(ray, col, row, start, cam, sph);
+            float len;
+            unsigned e = 0, s = 0;
+            bool cont = first_trip<N, COUNT>(ray, len, thr, rd, e, s);
+            if (COUNT && xok) { cR++; cE += e; cS += s; }
+            if (xok && !cont) *op = glsl_max(fadd(start, len), 0.0f);   // :84, :86
+            cont = cont && xok;
+            if (__any_sync(RTCE_FULL, cont)) {   // some lane needs a second trip
+                bool cont2 = false;
+                float last = len;   // len = 0 + last after the first trip
+                if (cont) {
+                    e = 0, s = 0;
+                    cont2 = march_step<N, COUNT>(ray, len, last, thr, rd, sph, e, s);
+                    if (COUNT) { cE += e; cS += s; }
+                    if (!cont2) *op = glsl_max(fadd(start, len), 0.0f);
+                }
+                const unsigned m2 = __ballot_sync(RTCE_FULL, cont2);
+                if (m2) {   // park the rays that need a third trip
+                    if (cont2) sq_push<N>(q, qn + __popc(m2 & lt), ray, len, last, start, (unsigned)(op - img));
+                    qn += __popc(m2);
+                    __syncwarp();
+                    if (qn >= 32) qn = tail_march<N, COUNT>(q, qn, false, img, thr, rd, sph, oq, oq_open, cE, cS, lane);
+                }
+            }
+            if (HAS_PARENT) {
+                if ((yb + rr) & 1) {   // next row starts a new pair
+                    start = ahead;
+                    if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
+                }
+            }
+        }
+        task = __shfl_sync(RTCE_FULL, next, 0);
+    }
+    if (P.dbg) t1 = globaltimer_ns();
+    if (qn > 0) qn = tail_march<N, COUNT>(q, qn, true, img, thr, rd, sph, oq, oq_open, cE, cS, lane);
+    if (P.dbg && lane == 0) {
+        unsigned long long* d = P.dbg + 4 * (size_t)(blockIdx.x * (kStripThreads / 32) + warp);
+        d[0] = t0; d[1] = t1; d[2] = globaltimer_ns(); d[3] = (unsigned long long)ndone;
+    }
+
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) {
+            cR += __shfl_down_sync(RTCE_FULL, cR, o);
+            cE += __shfl_down_sync(RTCE_FULL, cE, o);
+            cS += __shfl_down_sync(RTCE_FULL, cS, o);
+        }
+        if (lane == 0) {
+            atomicAdd(P.counters + 0, (unsigned long long)cR);
+            atomicAdd(P.counters + 1, (unsigned long long)cE);
+            atomicAdd(P.counters + 2, (unsigned long long)cS);
+        }
+    }
+}
+
+template <int N, bool COUNT, bool HAS_PARENT>
+static cudaError_t launch_strip_ncp(const StripParams& p, cudaStream_t st) {
+    const int smem = (kStripThreads / 32) * (RTCE_SQ_WORDS(N) * kQCap + 4 * kStripMaxRows + kPinWords) * (int)sizeof(float);
+    static bool configured = false;   // per instantiation
+    static int resident = 148 * 3;    // CTAs the device holds at once
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_trace_strip<N, COUNT, HAS_PARENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(k_trace_strip<N, COUNT, HAS_PARENT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+        if (e != cudaSuccess) return e;
+        int dev = 0, sms = 148, per_sm = 3;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_strip<N, COUNT, HAS_PARENT>, kStripThreads, smem);
+        if (e != cudaSuccess) return e;
+        resident = sms * (per_sm > 0 ? per_sm : 1);
+        configured = true;
+    }
+    // persistent CTAs: one resident wave for the whole batch
+    const long long tasks = (long long)p.ntx * p.nty * p.frames;
+    long long ctas = resident;
+    const long long need = (tasks + kStripThreads / 32 - 1) / (kStripThreads / 32);
+    if (ctas > need) ctas = need;
+    dim3 grid((unsigned)ctas, 1, 1);
+    k_trace_strip<N, COUNT, HAS_PARENT><<<grid, kStripThreads, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+template <int N>
+static cudaError_t launch_strip_n(const StripParams& p, bool count, cudaStream_t st) {
+    if (p.parent) return count ? launch_strip_ncp<N, true, true>(p, st) : launch_strip_ncp<N, false, true>(p, st);
+    return count ? launch_strip_ncp<N, true, false>(p, st) : launch_strip_ncp<N, false, false>(p, st);
+}
+
+cudaError_t launch_trace_strip(const StripParams& p, bool count, cudaStream_t st) {
+    if (p.frames <= 0 || p.ntx <= 0 || p.nty <= 0) return cudaSuccess;
+    if (p.rows < 1 || p.rows > kStripMaxRows || !(p.render_dist > 0.0f)) return cudaErrorInvalidValue;
+#ifdef RTCE_EXPERIMENT   // compile-time experiments: one instantiation only
+    return launch_strip_ncp<4, false, true>(p, st);
+#else
+    switch (p.n_spheres) {
+        case 0: return launch_strip_n<0>(p, count, st);
+        case 1: return launch_strip_n<1>(p, count, st);
+        case 2: return launch_strip_n<2>(p, count, st);
+        case 3: return launch_strip_n<3>(p, count, st);
+        case 4: return launch_strip_n<4>(p, count, st);
+        case 5: return launch_strip_n<5>(p, count, st);
+        case 6: return launch_strip_n<6>(p, count, st);
+        case 7: return launch_strip_n<7>(p, count, st);
+        case 8: return launch_strip_n<8>(p, count, st);
+        default: return cudaErrorInvalidValue;
+    }
+#endif
+}
+
+
+template <int N>
+static cudaError_t launch_overflow_n(const OverflowParams& p, bool count, cudaStream_t st) {
+    static int ctas = 0;
+    if (!ctas) {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        ctas = sms * 2;   // 16 warps per SM: the queue is short and latency-bound
+    }
+    if (count)
+        k_march_overflow<N, true><<<ctas, 256, 0, st>>>(p);
+    else
+        k_march_overflow<N, false><<<ctas, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_march_overflow(const OverflowParams& p, bool count, cudaStream_t st) {
+#ifdef RTCE_EXPERIMENT
+    return launch_overflow_n<4>(p, count, st);
+#else
+    switch (p.n_spheres) {
+        case 0: return cudaSuccess;   // no objects: every ray ends in its first trip
+        case 1: return launch_overflow_n<1>(p, count, st);
+        case 2: return launch_overflow_n<2>(p, count, st);
+        case 3: return launch_overflow_n<3>(p, count, st);
+        case 4: return launch_overflow_n<4>(p, count, st);
+        case 5: return launch_overflow_n<5>(p, count, st);
+        case 6: return launch_overflow_n<6>(p, count, st);
+        case 7: return launch_overflow_n<7>(p, count, st);
+        case 8: return launch_overflow_n<8>(p, count, st);
+        default: return cudaErrorInvalidValue;
+    }
+#endif
+}
+
+}  // namespace rtce

@@ -16,8 +16,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librtce.so")
 
 RTCE_OK = 0
-OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL = 1, 2, 3
-KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED = 0, 1, 2
+OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS = 1, 2, 3, 4, 5
+KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED, KERNEL_STRIP = 0, 1, 2, 3
 
 # compute.glsl:7-12 PushConstantData, 40 bytes
 PUSH_CONSTANTS_DTYPE = np.dtype(
@@ -32,7 +32,8 @@ EXPORTS = [
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
     "rtce_trace_accumulate", "rtce_accum_info", "rtce_readback", "rtce_readback_accum",
     "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_get_counters",
-    "rtce_measure_fp32_issue", "rtce_selftest_math",
+    "rtce_measure_fp32_issue", "rtce_selftest_math", "rtce_debug_strip_timeline",
+    "rtce_debug_launch_timeline",
 ]
 
 
@@ -88,6 +89,8 @@ def load_library() -> C.CDLL:
         "rtce_get_counters": (i32, [vp, C.POINTER(_Counters)]),
         "rtce_measure_fp32_issue": (i32, [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "rtce_selftest_math": (i32, [i32, C.POINTER(C.c_uint64)]),
+        "rtce_debug_strip_timeline": (i32, [vp, i32, vp, i32]),
+        "rtce_debug_launch_timeline": (i32, [vp, vp, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -291,6 +294,21 @@ class Engine:
         self._check(self.lib.rtce_render_to_host(self._ctx, pcs.ctypes.data, pcs.shape[0], out.ctypes.data),
                     "rtce_render_to_host")
         return out
+
+    def strip_timeline(self, level: int = -1, max_warps: int = 8192, fetch: bool = True):
+        """Diagnostics: arm / fetch the per-warp timeline of the strip launch that traces `level`."""
+        out = np.zeros((max_warps, 4), dtype=np.uint64)
+        self._check(self.lib.rtce_debug_strip_timeline(self._ctx, level, out.ctypes.data if fetch else None, max_warps),
+                    "rtce_debug_strip_timeline")
+        return out[out[:, 2] != 0]
+
+    def launch_timeline(self, fetch: bool = True, max_launches: int = 4096):
+        """Diagnostics: arm (fetch=False) / fetch the event timeline of the kernel launches since arming."""
+        out = np.zeros((max_launches, 6), dtype=np.float64)
+        n = self.lib.rtce_debug_launch_timeline(self._ctx, out.ctypes.data if fetch else None, max_launches)
+        if n < 0:
+            self._check(n, "rtce_debug_launch_timeline")
+        return out[:n]
 
     def counters(self) -> dict:
         c = _Counters()

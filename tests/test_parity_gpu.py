@@ -15,7 +15,17 @@ from raytracing_engine_b200 import camera, scene
 
 pytestmark = pytest.mark.gpu
 
-MODES = [rt.KERNEL_PER_LEVEL, rt.KERNEL_FUSED]
+# (kernel plan, strip threshold): per-pixel kernels; fused pyramid; strip kernel on EVERY level (threshold 0,
+# level 0 included); strip kernel on the larger levels over a fused-pyramid prefix; the shipped default
+MODES = [(rt.KERNEL_PER_LEVEL, None), (rt.KERNEL_FUSED, None), (rt.KERNEL_STRIP, 0), (rt.KERNEL_STRIP, 3000),
+         (rt.KERNEL_AUTO, None)]
+
+
+def _set_mode(e, mode):
+    kernel, min_rays = mode if isinstance(mode, tuple) else (mode, None)
+    e.set_option(rt.OPT_KERNEL, kernel)
+    if min_rays is not None:
+        e.set_option(rt.OPT_STRIP_MIN_RAYS, min_rays)
 
 
 def _bits(a):
@@ -25,7 +35,7 @@ def _bits(a):
 def _engine(case, mode=rt.KERNEL_AUTO, slots=None, count=False):
     (name, kind, sph, W, H, levels, rot, pos, keep) = case
     e = rt.Engine(0, 1000.0)
-    e.set_option(rt.OPT_KERNEL, mode)
+    _set_mode(e, mode)
     if slots:
         e.set_option(rt.OPT_FRAME_SLOTS, slots)
     if count:
@@ -75,7 +85,7 @@ def test_fuzz_against_cpu_checker(mode):
         levels = o.level_count(float(W), rule)
         ref, cnt = o.trace(sph, [W, H], scene.view_ratio(W, H), rot, pos, 1000.0, levels)
         with rt.Engine(0, 1000.0) as e:
-            e.set_option(rt.OPT_KERNEL, mode)
+            _set_mode(e, mode)
             e.set_option(rt.OPT_COUNTERS, 1)
             e.set_spheres(sph)
             e.set_view(W, H, levels=-1 if rule else 0)
