@@ -49,7 +49,8 @@ def parse_args():
     ap.add_argument("--levels", type=int, default=None, help="override pyramid levels (configs[3] sweep)")
     ap.add_argument("--kernel", type=int, default=0, help="0 auto (= 3), 1 per-pixel kernel per level, 2 fused pyramid kernel, 3 strip kernels + fused coarse levels")
     ap.add_argument("--strip-min-rays", type=int, default=None, help="kernel plan 3: strip-kernel threshold (rays per launch)")
-    ap.add_argument("--groups", type=int, default=None, help="kernel plan 3: frame groups per batch (1 or 2)")
+    ap.add_argument("--groups", type=int, default=None, help="kernel plan 3: frame groups per batch (1..8)")
+    ap.add_argument("--strip-rows", type=int, default=None, help="kernel plan 3: rows per strip task")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--profile", action="store_true", help="short run for ncu: no e2e, no CPU baseline, no clock hold")
@@ -233,6 +234,8 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_STRIP_MIN_RAYS, args.strip_min_rays)
     if args.groups is not None:
         eng.set_option(rt.OPT_GROUPS, args.groups)
+    if args.strip_rows is not None:
+        eng.set_option(rt.OPT_STRIP_ROWS, args.strip_rows)
     slots = min(frames, 16)
     eng.set_option(rt.OPT_FRAME_SLOTS, slots)
     if len(spheres) <= 8:
@@ -276,9 +279,11 @@ def run_ours(args, wl):
         else:
             eng.trace(pcs[: min(frames, slots)])
         cnt = eng.counters()
+        cnt_last = eng.level_counters(-1)
         eng.set_option(rt.OPT_COUNTERS, 0)
     scale = frames / min(frames, slots)   # static-pose workloads repeat the same frames
     cnt_step = {k: int(cnt[k] * scale) for k in "RES"}
+    cnt_last_step = {k: int(cnt_last[k] * scale) for k in "RES"}   # this rank's final-level launches
     if world > 1:
         t = torch.tensor([cnt_step["R"], cnt_step["E"], cnt_step["S"]], dtype=torch.int64, device=f"cuda:{local_rank}")
         dist.all_reduce(t)
@@ -323,6 +328,31 @@ def run_ours(args, wl):
         ms_total = float(t.item())
     ms_step = ms_total / steps
     value = units_per_step / (ms_step * 1e-3) / 1e6
+
+    # ---- the dominant kernel (the launch that traces the final level: 75 % of all rays), timed alone ----
+    # CUDA events around each of its launches (rtce_debug_launch_timeline), one frame group so that no
+    # other launch shares the machine with it, same workload, same warm state.
+    dom = None
+    if not wl["accumulate"] and len(spheres) <= 8:
+        with torch.cuda.stream(stream):
+            eng.set_option(rt.OPT_GROUPS, 1)
+            for _ in range(3):
+                step()
+            barrier()
+            eng.launch_timeline(fetch=False)
+            k_dom = max(3, min(steps, 20))
+            for _ in range(k_dom):
+                step()
+            tl = eng.launch_timeline(max_launches=4096)
+            eng.launch_timeline(max_launches=0)   # disarm
+            eng.set_option(rt.OPT_GROUPS, args.groups if args.groups is not None else 2)
+            barrier()
+        sel = tl[(tl[:, 2] == 1) & (tl[:, 3] == levels - 1)]
+        if len(sel):
+            dur = sel[:, 1] - sel[:, 0]
+            dom = {"kernel": "k_trace_strip (final pyramid level)", "launches_timed": int(len(sel)),
+                   "launches_per_step": int(len(sel) // k_dom), "ms_per_launch": float(dur.mean()),
+                   "ms_per_launch_min": float(dur.min()), "counters_per_launch": None}
 
     # ---- end to end through the public API with HOST buffers (push constants in, images out) ----
     e2e = None
@@ -371,18 +401,37 @@ def run_ours(args, wl):
     fp32_peak, fp32_ms = rt.measure_fp32_issue(local_rank, 4096)
     nominal = 148 * 128 * sm_max * 1e6
     achieved = ops_step / (ms_step * 1e-3)
-    roofline = {
-        "bound": "fp32_issue", "achieved": achieved / 1e12, "peak": fp32_peak * n_gpus / 1e12, "unit": "Tlane-op/s",
-        "frac": achieved / (fp32_peak * n_gpus), "traffic": None,
-        "peak_source": "measured live: rtce_measure_fp32_issue (non-contracted FMUL/FADD, register operands); "
-                       f"nominal 148 SM x 128 lanes x {sm_max:.0f} MHz = {nominal / 1e12:.1f}",
-        "frac_of_nominal": achieved / (nominal * n_gpus),
-        "ops_per_step": ops_step, "counters_per_step": cnt_step,
-        "scope": "all kernels of the step (launch gaps included)",
-        "hbm": {"achieved": bytes_step / (ms_step * 1e-3) / 1e9, "peak": hbm_peak * n_gpus, "unit": "GB/s",
-                "frac": bytes_step / (ms_step * 1e-3) / 1e9 / (hbm_peak * n_gpus), "peak_source": peak_src + " MEASURED_PEAKS.json",
-                "bytes_per_step": bytes_step},
-    }
+    step_achieved = ops_step / (ms_step * 1e-3)
+    step_roof = {"achieved": step_achieved / 1e12, "frac": step_achieved / (fp32_peak * n_gpus),
+                 "frac_of_nominal": step_achieved / (nominal * n_gpus), "ops_per_step": ops_step,
+                 "counters_per_step": cnt_step, "scope": "all launches of the step, gaps included",
+                 "hbm": {"achieved": bytes_step / (ms_step * 1e-3) / 1e9, "peak": hbm_peak * n_gpus, "unit": "GB/s",
+                         "frac": bytes_step / (ms_step * 1e-3) / 1e9 / (hbm_peak * n_gpus),
+                         "peak_source": peak_src + " MEASURED_PEAKS.json", "bytes_per_step": bytes_step}}
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "dominant_kernel_ncu.json")
+    if os.path.exists(tp):
+        with open(tp) as fh:
+            traffic = json.load(fh).get("dram_bytes_per_launch")
+    peak_note = ("measured live: rtce_measure_fp32_issue (non-contracted FMUL/FADD, register operands); "
+                 f"nominal 148 SM x 128 lanes x {sm_max:.0f} MHz = {nominal / 1e12:.1f}")
+    if dom is not None:
+        ops_launch = algorithmic_ops(cnt_last_step, len(spheres)) / dom["launches_per_step"]
+        dom["counters_per_launch"] = {k: cnt_last_step[k] // dom["launches_per_step"] for k in "RES"}
+        achieved = ops_launch / (dom["ms_per_launch"] * 1e-3)
+        roofline = {"bound": "fp32_issue", "achieved": achieved / 1e12, "peak": fp32_peak / 1e12, "unit": "Tlane-op/s",
+                    "frac": achieved / fp32_peak, "traffic": traffic, "peak_source": peak_note,
+                    "frac_of_nominal": achieved / nominal, "ops_per_launch": ops_launch,
+                    "scope": "dominant kernel: algorithmic FP32 operations (SURVEY.md 8d: 57 R + 10 E + (12 + 3 N) S, from "
+                             "the device's own work counters of the final level) per launch / its mean launch duration "
+                             "(CUDA events on its stream, one frame group, this rank)",
+                    "dominant_kernel": dom, "step": step_roof}
+    else:
+        roofline = {"bound": "fp32_issue", "achieved": step_achieved / 1e12, "peak": fp32_peak * n_gpus / 1e12,
+                    "unit": "Tlane-op/s", "frac": step_achieved / (fp32_peak * n_gpus), "traffic": traffic,
+                    "peak_source": peak_note, "frac_of_nominal": step_achieved / (nominal * n_gpus),
+                    "scope": "all launches of the step, gaps included (no single dominant launch was timed)",
+                    "step": step_roof}
 
     cpu_baseline = None
     if not args.no_cpu_baseline and n_gpus == 1:

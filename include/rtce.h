@@ -94,8 +94,12 @@ typedef enum rtce_option {
                                    3 = strip kernel per large level + fused-pyramid kernel for the coarse levels */
     RTCE_OPT_STRIP_MIN_RAYS = 4,/* kernel plan 3: a level is traced by the strip kernel when it has at least this
                                    many rays per launch (level pixels x frames of the launch), default 400000 */
-    RTCE_OPT_GROUPS = 5         /* kernel plan 3: 1 = one launch chain per batch, 2 (default) = the batch's frames in
-                                   two groups on two streams so that latency-bound launches overlap issue-bound ones */
+    RTCE_OPT_COARSE_FUSED = 6,  /* kernel plan 3: 1 = the levels below the strip threshold in one fused-pyramid launch,
+                                   0 (default) = one latency-oriented per-pixel launch per level */
+    RTCE_OPT_STRIP_ROWS = 7,    /* kernel plan 3: rows of a strip-kernel task (a task is 32 columns x this many rows), 1..32 */
+    RTCE_OPT_GROUPS = 5         /* kernel plan 3: number of frame groups (1..8, default 2) a batch is split into; every
+                                   group runs its launch chain on its own stream so that latency-bound launches of one
+                                   group overlap issue-bound launches of the others */
 } rtce_option;
 
 /* -- lifetime ------------------------------------------------------------------------------
@@ -157,6 +161,9 @@ int rtce_host_alloc(void** out, size_t nbytes);
 int rtce_host_free(void* p);
 int rtce_sync(rtce_ctx* ctx);                        /* fence wait, main.rs:882-884 */
 int rtce_get_counters(rtce_ctx* ctx, rtce_counters* out);
+/* The same per pyramid level (negative = from the last).  A fused-pyramid launch books all the levels it
+ * traces under its finest one. */
+int rtce_get_level_counters(rtce_ctx* ctx, int level, rtce_counters* out);
 
 /* -- measurement support (no reference counterpart) ---------------------------------------------
  * Sustained FP32 CUDA-core issue rate of `device`: a register-only kernel of independent,

@@ -16,7 +16,8 @@
 
 using namespace rtce;
 
-static constexpr unsigned kOverflowCap = 1u << 19;   // rays per frame group; 2 x 38 MB
+static constexpr int kMaxGroups = 8;
+static constexpr unsigned kOverflowCap = 1u << 17;   // rays per frame group (9.4 MB each); beyond it long rays stay in their warp
 
 struct rtce_ctx {
     int device = 0;
@@ -24,9 +25,11 @@ struct rtce_ctx {
     cudaStream_t own_stream = nullptr;   // created by rtce_create
     cudaStream_t stream = nullptr;       // the stream work is issued on (own_stream or the caller's)
     cudaStream_t copy_stream = nullptr;  // D2H copies of rtce_render_to_host
-    cudaStream_t aux_stream = nullptr;   // second frame group of a chunk (lower priority; forked from / joined to `stream`)
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    cudaStream_t grp_stream[kMaxGroups] = {};   // one per frame group of a chunk, forked from / joined to `stream`
+    cudaEvent_t ev_fork = nullptr, ev_join[kMaxGroups] = {};
     int groups = 2;                      // RTCE_OPT_GROUPS
+    bool coarse_fused = false;           // RTCE_OPT_COARSE_FUSED
+    int strip_rows = 16;                 // RTCE_OPT_STRIP_ROWS
     // diagnostics (rtce_debug_launch_timeline): an event pair around every kernel launch
     struct LaunchMark { cudaEvent_t e0, e1; int kind, level, group; };
     bool mark_launches = false;
@@ -150,16 +153,17 @@ int rtce_create(int device, float render_dist, rtce_ctx** out) {
     c->device = device;
     c->render_dist = render_dist;
     DeviceGuard g(device);
-    int prio_lo = 0, prio_hi = 0;
-    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);   // lo = numerically greatest = least urgent
-    if (cudaStreamCreateWithPriority(&c->own_stream, cudaStreamNonBlocking, prio_hi) != cudaSuccess ||
-        cudaStreamCreateWithPriority(&c->aux_stream, cudaStreamNonBlocking, prio_lo) != cudaSuccess ||
+    bool grp_ok = true;
+    for (int g = 0; g < kMaxGroups; g++) {
+        grp_ok = grp_ok && cudaStreamCreateWithFlags(&c->grp_stream[g], cudaStreamNonBlocking) == cudaSuccess &&
+                 cudaEventCreateWithFlags(&c->ev_join[g], cudaEventDisableTiming) == cudaSuccess;
+    }
+    if (!grp_ok || cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMalloc(&c->d_counters, 4 * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaMalloc(&c->d_tickets, sizeof(int) * 2 * kMaxLevels * 4) != cudaSuccess ||
-        cudaMalloc(&c->d_oq, sizeof(float) * 2 * (size_t)kOverflowCap * (10 + kSmallSceneMax)) != cudaSuccess) {
+        cudaMalloc(&c->d_counters, 4 * kMaxLevels * sizeof(unsigned long long)) != cudaSuccess ||
+        cudaMalloc(&c->d_tickets, sizeof(int) * kMaxGroups * kMaxLevels * 4) != cudaSuccess ||
+        cudaMalloc(&c->d_oq, sizeof(float) * kMaxGroups * (size_t)kOverflowCap * (10 + kSmallSceneMax)) != cudaSuccess) {
         rtce_destroy(c);
         return RTCE_ERR_CUDA;
     }
@@ -177,9 +181,11 @@ void rtce_destroy(rtce_ctx* c) {
     DeviceGuard g(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
-    if (c->aux_stream) cudaStreamSynchronize(c->aux_stream);
+    for (int g = 0; g < kMaxGroups; g++) {
+        if (c->grp_stream[g]) cudaStreamSynchronize(c->grp_stream[g]);
+        if (c->ev_join[g]) cudaEventDestroy(c->ev_join[g]);
+    }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    if (c->ev_join) cudaEventDestroy(c->ev_join);
     for (int i = 0; i < 2; i++) {
         if (c->ev_traced[i]) cudaEventDestroy(c->ev_traced[i]);
         if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
@@ -193,7 +199,8 @@ void rtce_destroy(rtce_ctx* c) {
     if (c->d_dbg) cudaFree(c->d_dbg);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
-    if (c->aux_stream) cudaStreamDestroy(c->aux_stream);
+    for (int g = 0; g < kMaxGroups; g++)
+        if (c->grp_stream[g]) cudaStreamDestroy(c->grp_stream[g]);
     delete c;
 }
 
@@ -213,8 +220,15 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             if (value < 0 || value > 3) return fail(c, RTCE_ERR_INVALID, "kernel mode out of range");
             c->kernel_mode = (int)value;
             return RTCE_OK;
+        case RTCE_OPT_STRIP_ROWS:
+            if (value < 1 || value > kStripMaxRows) return fail(c, RTCE_ERR_INVALID, "strip rows out of range");
+            c->strip_rows = (int)value;
+            return RTCE_OK;
+        case RTCE_OPT_COARSE_FUSED:
+            c->coarse_fused = value != 0;
+            return RTCE_OK;
         case RTCE_OPT_GROUPS:
-            if (value < 1 || value > 2) return fail(c, RTCE_ERR_INVALID, "groups out of range");
+            if (value < 1 || value > kMaxGroups) return fail(c, RTCE_ERR_INVALID, "groups out of range");
             c->groups = (int)value;
             return RTCE_OK;
         case RTCE_OPT_STRIP_MIN_RAYS:

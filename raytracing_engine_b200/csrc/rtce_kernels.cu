@@ -7,8 +7,7 @@
 //
 // Arithmetic: rtce_device.cuh (canonical, non-contracted).  Built with --fmad=false as a
 // second line of defence; no -use_fast_math.
-#include "rtce_device.cuh"
-#include "rtce_kernels.cuh"
+#include "rtce_march.cuh"
 
 namespace rtce {
 
@@ -129,6 +128,76 @@ cudaError_t launch_trace_level_small(const LevelParams& p, int frames, bool coun
         case 6: return launch_small_n<6>(p, frames, count, st);
         case 7: return launch_small_n<7>(p, frames, count, st);
         case 8: return launch_small_n<8>(p, frames, count, st);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Coarse levels (a few thousand rays per frame, but up to ~40 dependent march trips per ray): one
+// thread per pixel, 8x4 pixels per warp, marched to the end in place with the branch-free trip
+// (march_step_pred) — these launches are bound by the latency of the longest ray, not by issue.
+// Requires RENDER_DIST > 0.
+// ------------------------------------------------------------------------------------------
+template <int N, bool COUNT>
+__global__ void __launch_bounds__(256)
+    k_trace_level_pix(const __grid_constant__ LevelParams P) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x = P.x0 + blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
+    const int y = P.y0 + blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
+    const int f = blockIdx.z;
+    unsigned cR = 0, cE = 0, cS = 0;
+    if (x < P.x1 && y < P.y1) {
+        const Cam& cam = P.cam[f];
+        const float4 col = col_terms(cam, norm_coord(x, P.isx, P.ratx));
+        const float4 row = row_terms(cam, norm_coord(y, P.isy, P.raty));
+        float start = 1.0f;   // compute.glsl:79
+        if (P.iter > 0) start = __ldg(P.parent + (size_t)f * P.slot_stride + (size_t)(y >> 1) * (size_t)P.pw + (size_t)(x >> 1));
+        Ray<N> ray;
+        ray_setup<N>(ray, col, row, start, cam, P.sph);
+        float len = 0.0f;
+        bool go = first_step<N, COUNT>(ray, len, P.threshold, P.render_dist, cE, cS);
+        float last = len;
+        while (go) go = march_step_pred<N, COUNT>(ray, len, last, P.threshold, P.render_dist, P.sph, cE, cS);
+        P.out[(size_t)f * P.slot_stride + (size_t)y * (size_t)P.w + (size_t)x] = glsl_max(fadd(start, len), 0.0f);   // :84, :86
+        cR = 1;
+    }
+    if (COUNT) {
+        for (int o = 16; o > 0; o >>= 1) {
+            cR += __shfl_down_sync(0xffffffffu, cR, o);
+            cE += __shfl_down_sync(0xffffffffu, cE, o);
+            cS += __shfl_down_sync(0xffffffffu, cS, o);
+        }
+        if (lane == 0) {
+            atomicAdd(P.counters + 0, (unsigned long long)cR);
+            atomicAdd(P.counters + 1, (unsigned long long)cE);
+            atomicAdd(P.counters + 2, (unsigned long long)cS);
+        }
+    }
+}
+
+template <int N>
+static cudaError_t launch_pix_n(const LevelParams& p, int frames, bool count, cudaStream_t st) {
+    dim3 grid((unsigned)((p.x1 - p.x0 + 31) / 32), (unsigned)((p.y1 - p.y0 + 7) / 8), (unsigned)frames);
+    if (count)
+        k_trace_level_pix<N, true><<<grid, 256, 0, st>>>(p);
+    else
+        k_trace_level_pix<N, false><<<grid, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_trace_level_pix(const LevelParams& p, int frames, bool count, cudaStream_t st) {
+    if (p.x1 <= p.x0 || p.y1 <= p.y0 || frames <= 0) return cudaSuccess;
+    if (!(p.render_dist > 0.0f)) return cudaErrorInvalidValue;
+    switch (p.n_spheres) {
+        case 0: return launch_pix_n<0>(p, frames, count, st);
+        case 1: return launch_pix_n<1>(p, frames, count, st);
+        case 2: return launch_pix_n<2>(p, frames, count, st);
+        case 3: return launch_pix_n<3>(p, frames, count, st);
+        case 4: return launch_pix_n<4>(p, frames, count, st);
+        case 5: return launch_pix_n<5>(p, frames, count, st);
+        case 6: return launch_pix_n<6>(p, frames, count, st);
+        case 7: return launch_pix_n<7>(p, frames, count, st);
+        case 8: return launch_pix_n<8>(p, frames, count, st);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -39,6 +39,9 @@ struct LevelParams {
 
 // Per-level kernel, objCount <= 8 (one thread per pixel, frames in grid.z).
 cudaError_t launch_trace_level_small(const LevelParams& p, int frames, bool count, cudaStream_t st);
+// Same dispatch for the coarse, latency-bound levels: 8x4 pixels per warp, branch-free march trips,
+// short correctly rounded sqrt.  Requires RENDER_DIST > 0.
+cudaError_t launch_trace_level_pix(const LevelParams& p, int frames, bool count, cudaStream_t st);
 
 // Large scenes (objCount > 8): spheres in global memory, one CTA per ray.
 struct LevelParamsLarge {
@@ -115,6 +118,7 @@ struct StripParams {
     int x0, y0, x1, y1;       // region of interest at this level
     int ntx, nty;             // tasks per frame: 32-wide columns x `rows`-high rows covering the ROI
     int rows;                 // rows per task, 1..kStripMaxRows
+    int cta_share;            // launch 1/cta_share of the resident CTA slots (>= 1)
     int frames;
     int n_spheres;
     float isx, isy, ratx, raty, threshold, render_dist;

@@ -166,7 +166,7 @@ RTCE_DEV int tail_march(float* q, int qn, const bool drain, float* __restrict__ 
 
 // The overflow queue of one strip launch, marched to the end by every warp of the device.
 template <int N, bool COUNT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
     k_march_overflow(const __grid_constant__ OverflowParams P) {
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -201,7 +201,7 @@ __global__ void __launch_bounds__(256)
         }
         if (active) {
             unsigned e = 0, s = 0;
-            const bool go = march_step<N, COUNT>(r, len, last, thr, rd, sph, e, s);
+            const bool go = march_step_pred<N, COUNT>(r, len, last, thr, rd, sph, e, s);
             if (COUNT) { cE += e; cS += s; }
             if (!go) {
                 img[off] = glsl_max(fadd(start, len), 0.0f);   // compute.glsl:84, :86
@@ -294,18 +294,45 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
     int qn = 0;   // warp-uniform
 
     // Tasks (frame-major) are handed out dynamically, one atomic per task fetched one task ahead:
-    // march cost differs by > 2x between tiles that cover spheres and tiles that see only
-    // background, and between the frames of a batch.
-    int task = blockIdx.x * (kStripThreads / 32) + warp;   // the first round is static
+    // march cost differs by > 5x between tiles that cover spheres and tiles that see only
+    // background.  With a parent level the ticket range is walked TWICE: the first pass takes only
+    // the tiles whose parent texels show a hit ("hot": second trips, tail marches), the second pass
+    // the rest, whose cost is small and uniform, so the launch ends without a ragged tail of
+    // expensive tiles (longest-processing-time-first scheduling with a two-class estimate).
+    const int tickets_total = HAS_PARENT ? 2 * tasks : tasks;
+    int ticket = blockIdx.x * (kStripThreads / 32) + warp;   // the first round is static
     int next = 0;
     unsigned long long t0 = 0, t1 = 0;
     int ndone = 0;
     if (P.dbg) t0 = globaltimer_ns();
-    while (task < tasks) {
-        ndone++;
+    while (ticket < tickets_total) {
         if (lane == 0) next = atomicAdd(P.tickets, 1) + nwarps;
+        const int second = ticket >= tasks ? 1 : 0;
+        const int task = ticket - second * tasks;
         const int f = task / tiles, tile = task - f * tiles;
         const int ty = tile / P.ntx, tx = tile - ty * P.ntx;
+        const int x = P.x0 + tx * 32 + lane;
+        const bool xok = x < P.x1;
+        const int xc = min(x, P.x1 - 1);   // lanes past the region repeat its last column and store nothing
+        const int yb = P.y0 + ty * P.rows;
+        const int rows = min(P.rows, P.y1 - yb);
+        // :80-82  rows 2k and 2k+1 share the parent texel; it is fetched one row pair ahead
+        const float* pp = nullptr;
+        float start = 1.0f, ahead = 0.0f;   // compute.glsl:79
+        int pairs_left = 0;                 // parent rows still to fetch after `ahead`
+        if (HAS_PARENT) {
+            pp = P.parent + ((size_t)f * P.slot_stride + (size_t)(yb >> 1) * P.pw + (xc >> 1));
+            pairs_left = ((yb + rows - 1) >> 1) - (yb >> 1);
+            start = __ldg(pp);
+            const float bottom = __ldg(pp + (size_t)pairs_left * P.pw);
+            const int hot = __any_sync(RTCE_FULL, start < rd || bottom < rd) ? 1 : 0;   // a parent ray stopped on a sphere
+            if (hot == second) {   // not this pass's class
+                ticket = __shfl_sync(RTCE_FULL, next, 0);
+                continue;
+            }
+            if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
+        }
+        ndone++;
         Cam cam;
         {
             const Cam& c0 = P.cam[f];
@@ -320,26 +347,11 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
             for (int i = 0; i < 3; i++) cam.pos[i] = pin[4 + i];
             cam.pad = 0.0f;
         }
-        const int x = P.x0 + tx * 32 + lane;
-        const bool xok = x < P.x1;
-        const int xc = min(x, P.x1 - 1);   // lanes past the region repeat its last column and store nothing
-        const int yb = P.y0 + ty * P.rows;
-        const int rows = min(P.rows, P.y1 - yb);
         const float4 col = col_terms(cam, norm_coord(xc, P.isx, P.ratx));
         __syncwarp();   // the previous task's table reads are done
         if (lane < rows) rowtab[lane] = row_terms(cam, norm_coord(yb + lane, P.isy, P.raty));
         __syncwarp();
         float* op = img + ((size_t)f * P.slot_stride + (size_t)yb * P.w + xc);   // this lane's texel, row by row
-        // :80-82  rows 2k and 2k+1 share the parent texel; it is fetched one row pair ahead
-        const float* pp = nullptr;
-        float start = 1.0f, ahead = 0.0f;   // compute.glsl:79
-        int pairs_left = 0;                 // parent rows still to fetch after `ahead`
-        if (HAS_PARENT) {
-            pp = P.parent + ((size_t)f * P.slot_stride + (size_t)(yb >> 1) * P.pw + (xc >> 1));
-            pairs_left = ((yb + rows - 1) >> 1) - (yb >> 1);
-            start = __ldg(pp);
-            if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
-        }
         for (int rr = 0; rr < rows; rr++, op += P.w) {
             const float4 row = rowtab[rr];
             Ray<N> ray;
@@ -374,7 +386,7 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
                 }
             }
         }
-        task = __shfl_sync(RTCE_FULL, next, 0);
+        ticket = __shfl_sync(RTCE_FULL, next, 0);
     }
     if (P.dbg) t1 = globaltimer_ns();
     if (qn > 0) qn = tail_march<N, COUNT>(q, qn, true, img, thr, rd, sph, oq, oq_open, cE, cS, lane);
@@ -417,7 +429,8 @@ static cudaError_t launch_strip_ncp(const StripParams& p, cudaStream_t st) {
     }
     // persistent CTAs: one resident wave for the whole batch
     const long long tasks = (long long)p.ntx * p.nty * p.frames;
-    long long ctas = resident;
+    long long ctas = resident / (p.cta_share > 1 ? p.cta_share : 1);
+    if (ctas < 1) ctas = 1;
     const long long need = (tasks + kStripThreads / 32 - 1) / (kStripThreads / 32);
     if (ctas > need) ctas = need;
     dim3 grid((unsigned)ctas, 1, 1);
@@ -460,12 +473,13 @@ static cudaError_t launch_overflow_n(const OverflowParams& p, bool count, cudaSt
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        ctas = sms * 2;   // 16 warps per SM: the queue is short and latency-bound
+        ctas = sms;   // one warp per scheduler: every trip runs at the latency of its dependent chain, and a
+                      // 128-thread CTA fits beside three resident strip CTAs
     }
     if (count)
-        k_march_overflow<N, true><<<ctas, 256, 0, st>>>(p);
+        k_march_overflow<N, true><<<ctas, 128, 0, st>>>(p);
     else
-        k_march_overflow<N, false><<<ctas, 256, 0, st>>>(p);
+        k_march_overflow<N, false><<<ctas, 128, 0, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -229,4 +229,37 @@ RTCE_DEV bool march_step(Ray<N>& r, float& len, float& last, const float thresho
     return len < rd;               // :44
 }
 
+// march_step with a branch-free refresh: the exact SDF of EVERY object is evaluated (N independent
+// chains that depend only on `len`) and selected where the cached bound fell inside the cone.  Same
+// values as march_step (a refresh that is not selected has no effect), ~2x the instructions, but
+// the dependent chain of one trip drops from N serial branch-and-refresh blocks to one SDF chain.
+// Used where marching is latency-bound (long rays, coarse levels), not in the issue-bound kernels.
+template <int N, bool COUNT>
+RTCE_DEV bool march_step_pred(Ray<N>& r, float& len, float& last, const float threshold, const float rd,
+                              const float4* __restrict__ sph, unsigned& cE, unsigned& cS) {
+    const float px = fadd(r.ox, fmul(r.sx, len));   // :45
+    const float py = fadd(r.oy, fmul(r.sy, len));
+    const float pz = fadd(r.oz, fmul(r.sz, len));
+    float dist = rd;                                           // :49
+    const float radius = fmul(fadd(len, 1.0f), threshold);    // :50
+#pragma unroll
+    for (int i = 0; i < N; i++) {   // :51-57
+        const float dx = fsub(px, sph[i].x), dy = fsub(py, sph[i].y), dz = fsub(pz, sph[i].z);
+        const float exact = fsub(sqrt_fast(fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz))), sph[i].w);
+        const float bound = fsub(r.d[i], last);
+        const bool refresh = bound <= radius;
+        if (COUNT) cE += refresh ? 1u : 0u;
+        r.d[i] = refresh ? exact : bound;
+        dist = glsl_min(dist, r.d[i]);
+    }
+    if (COUNT) cS++;
+    last = glsl_max(dist, 0.0f);   // :59
+    len = fadd(len, last);         // :60
+    if (dist <= radius) {          // :62-65
+        len = fsub(len, radius);
+        return false;
+    }
+    return len < rd;               // :44
+}
+
 }  // namespace rtce

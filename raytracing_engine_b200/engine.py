@@ -16,7 +16,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librtce.so")
 
 RTCE_OK = 0
-OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS = 1, 2, 3, 4, 5
+OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS, OPT_COARSE_FUSED, OPT_STRIP_ROWS = 1, 2, 3, 4, 5, 6, 7
 KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED, KERNEL_STRIP = 0, 1, 2, 3
 
 # compute.glsl:7-12 PushConstantData, 40 bytes
@@ -32,6 +32,7 @@ EXPORTS = [
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
     "rtce_trace_accumulate", "rtce_accum_info", "rtce_readback", "rtce_readback_accum",
     "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_get_counters",
+    "rtce_get_level_counters",
     "rtce_measure_fp32_issue", "rtce_selftest_math", "rtce_debug_strip_timeline",
     "rtce_debug_launch_timeline",
 ]
@@ -87,6 +88,7 @@ def load_library() -> C.CDLL:
         "rtce_host_free": (i32, [vp]),
         "rtce_sync": (i32, [vp]),
         "rtce_get_counters": (i32, [vp, C.POINTER(_Counters)]),
+        "rtce_get_level_counters": (i32, [vp, i32, C.POINTER(_Counters)]),
         "rtce_measure_fp32_issue": (i32, [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "rtce_selftest_math": (i32, [i32, C.POINTER(C.c_uint64)]),
         "rtce_debug_strip_timeline": (i32, [vp, i32, vp, i32]),
@@ -309,6 +311,11 @@ class Engine:
         if n < 0:
             self._check(n, "rtce_debug_launch_timeline")
         return out[:n]
+
+    def level_counters(self, level: int = -1) -> dict:
+        c = _Counters()
+        self._check(self.lib.rtce_get_level_counters(self._ctx, level, C.byref(c)), "rtce_get_level_counters")
+        return {"R": int(c.rays), "E": int(c.sdf_evals), "S": int(c.march_steps)}
 
     def counters(self) -> dict:
         c = _Counters()
