@@ -171,7 +171,10 @@ __global__ void __launch_bounds__(128)
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
     const unsigned n = min(*P.oq_count, P.oq_cap);
-    if (n == 0u) return;
+    // Warps in use grow with the queue (~48 rays each, refilled as rays finish): a short queue is
+    // bound by the dependent chain of its longest ray and runs fastest with one warp per
+    // scheduler; a long one is issue-bound and wants them all.
+    if ((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 48u >= n) return;
     float4 sph[N > 0 ? N : 1];
 #pragma unroll
     for (int i = 0; i < N; i++) sph[i] = P.sph[i];
@@ -473,8 +476,8 @@ static cudaError_t launch_overflow_n(const OverflowParams& p, bool count, cudaSt
         int dev = 0, sms = 148;
         cudaGetDevice(&dev);
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        ctas = sms;   // one warp per scheduler: every trip runs at the latency of its dependent chain, and a
-                      // 128-thread CTA fits beside three resident strip CTAs
+        ctas = sms * 2;   // up to two warps per scheduler (see the kernel); a 128-thread CTA fits beside three
+                          // resident strip CTAs
     }
     if (count)
         k_march_overflow<N, true><<<ctas, 128, 0, st>>>(p);

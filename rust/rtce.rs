@@ -1,0 +1,160 @@
+//! rtce.rs — Rust binding of the C ABI in include/rtce.h (librtce.so), for the reference's host
+//! (IvoteSligte/raytracing_engine, src/main.rs).  SOURCE ONLY: this image has no rustc/cargo and
+//! the reference itself does not build outside its author's machine (Cargo.toml:9 is a local
+//! Windows path dependency), so the ABI is exercised from Python/ctypes and C++ in tests/.
+//!
+//! The #[repr(C)] structs are byte-for-byte the types vulkano-shaders generates from the GLSL
+//! (`shaders::ty::*`, src/main.rs:47-66), so the values src/main.rs already builds at
+//! :524-629 can be passed through unchanged.
+#![allow(non_camel_case_types, non_snake_case, dead_code)]
+
+use std::ffi::CStr;
+use std::os::raw::{c_char, c_int, c_void};
+
+/// compute.glsl:7-12 PushConstantData, 40 bytes (src/main.rs:301-307, 624-629, 770-773).
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct PushConstantData {
+    pub rot: [f32; 4],       // glam Quat::to_array() = [x, y, z, w]
+    pub pos: [f32; 3],
+    pub iter: u32,           // filled per level by the library (main.rs:302)
+    pub imageSize: [f32; 2], // filled per level by the library (main.rs:303-305)
+}
+
+/// compute.glsl:26-29 ConstantBuffer, 16 bytes (src/main.rs:608-611).
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct ConstantBuffer {
+    pub view: [f32; 2],
+    pub ratio: [f32; 2],
+}
+
+/// utilities.glsl:16-19 Object = one element of MutableData.objs.
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct Sphere {
+    pub pos: [f32; 3],
+    pub size: f32,
+}
+
+#[repr(C)]
+#[derive(Clone, Copy, Debug, Default)]
+pub struct Counters {
+    pub rays: u64,
+    pub sdf_evals: u64,
+    pub march_steps: u64,
+    pub kernel_launches: u64,
+}
+
+#[repr(C)]
+pub struct rtce_ctx {
+    _private: [u8; 0],
+}
+
+pub const RTCE_MUTABLE_DATA_SIZE: usize = 656;
+
+#[link(name = "rtce")]
+extern "C" {
+    fn rtce_abi_version() -> c_int;
+    fn rtce_create(device: c_int, render_dist: f32, out: *mut *mut rtce_ctx) -> c_int;
+    fn rtce_destroy(ctx: *mut rtce_ctx);
+    fn rtce_last_error(ctx: *const rtce_ctx) -> *const c_char;
+    fn rtce_status_string(status: c_int) -> *const c_char;
+    fn rtce_set_option(ctx: *mut rtce_ctx, option: c_int, value: i64) -> c_int;
+    fn rtce_set_scene(ctx: *mut rtce_ctx, mutable_data_std140: *const c_void, nbytes: usize) -> c_int;
+    fn rtce_set_spheres(ctx: *mut rtce_ctx, spheres: *const Sphere, n: u32) -> c_int;
+    fn rtce_set_view(ctx: *mut rtce_ctx, cb: *const ConstantBuffer, levels: c_int) -> c_int;
+    fn rtce_set_rect(ctx: *mut rtce_ctx, x0: c_int, y0: c_int, x1: c_int, y1: c_int) -> c_int;
+    fn rtce_level_count(ctx: *const rtce_ctx) -> c_int;
+    fn rtce_level_info(ctx: *const rtce_ctx, level: c_int, slot: c_int, w: *mut c_int, h: *mut c_int,
+                       device_ptr: *mut *mut f32) -> c_int;
+    fn rtce_trace(ctx: *mut rtce_ctx, pc: *const PushConstantData) -> c_int;
+    fn rtce_trace_batch(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int) -> c_int;
+    fn rtce_readback(ctx: *mut rtce_ctx, level: c_int, slot: c_int, host: *mut f32, pitch_bytes: usize) -> c_int;
+    fn rtce_render_to_host(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int, host_out: *mut f32) -> c_int;
+    fn rtce_sync(ctx: *mut rtce_ctx) -> c_int;
+    fn rtce_get_counters(ctx: *mut rtce_ctx, out: *mut Counters) -> c_int;
+}
+
+#[derive(Debug)]
+pub struct Error {
+    pub status: i32,
+    pub message: String,
+}
+
+/// Owns one context = one GPU, one stream; replaces the compute pipeline, its descriptor set and
+/// the pyramid images of src/main.rs:154-266, 631-662.
+pub struct ConeMarcher {
+    ctx: *mut rtce_ctx,
+}
+
+impl ConeMarcher {
+    /// Device selection + compute pipeline with the RENDER_DIST specialization constant
+    /// (src/main.rs:68-92, 450-460, 631-637).
+    pub fn new(device: i32, render_dist: f32) -> Result<Self, Error> {
+        let mut ctx: *mut rtce_ctx = std::ptr::null_mut();
+        let st = unsafe { rtce_create(device, render_dist, &mut ctx) };
+        if st != 0 {
+            let msg = unsafe { CStr::from_ptr(rtce_status_string(st)) }.to_string_lossy().into_owned();
+            return Err(Error { status: st, message: msg });
+        }
+        Ok(ConeMarcher { ctx })
+    }
+
+    fn check(&self, st: c_int) -> Result<(), Error> {
+        if st == 0 {
+            return Ok(());
+        }
+        let msg = unsafe { CStr::from_ptr(rtce_last_error(self.ctx)) }.to_string_lossy().into_owned();
+        Err(Error { status: st, message: msg })
+    }
+
+    /// Binding 1: `DeviceLocalBuffer::from_data(mutable_data)` (src/main.rs:592-605).  Pass
+    /// `bytemuck::bytes_of(&mutable_data)`.
+    pub fn set_scene(&mut self, mutable_data: &[u8]) -> Result<(), Error> {
+        let st = unsafe { rtce_set_scene(self.ctx, mutable_data.as_ptr() as *const c_void, mutable_data.len()) };
+        self.check(st)
+    }
+
+    /// Binding 2 + the pyramid (src/main.rs:608-615, 639-648); `levels = 0` = the startup rule
+    /// (main.rs:639), `-1` = the rule after a resize (main.rs:845).
+    pub fn set_view(&mut self, cb: &ConstantBuffer, levels: i32) -> Result<(), Error> {
+        let st = unsafe { rtce_set_view(self.ctx, cb, levels) };
+        self.check(st)
+    }
+
+    /// The compute half of `get_command_buffer` + submit (src/main.rs:291-316, 909-914).
+    pub fn trace(&mut self, pc: &PushConstantData) -> Result<(), Error> {
+        let st = unsafe { rtce_trace(self.ctx, pc) };
+        self.check(st)
+    }
+
+    pub fn trace_batch(&mut self, pcs: &[PushConstantData]) -> Result<(), Error> {
+        let st = unsafe { rtce_trace_batch(self.ctx, pcs.as_ptr(), pcs.len() as c_int) };
+        self.check(st)
+    }
+
+    /// What the fragment pass reads (src/main.rs:650-655 -> fragment.glsl:15,135): the last level.
+    pub fn final_level(&mut self, slot: i32) -> Result<(usize, usize, Vec<f32>), Error> {
+        let (mut w, mut h) = (0, 0);
+        let mut p: *mut f32 = std::ptr::null_mut();
+        let st = unsafe { rtce_level_info(self.ctx, -1, slot, &mut w, &mut h, &mut p) };
+        self.check(st)?;
+        let mut out = vec![0f32; (w * h) as usize];
+        let st = unsafe { rtce_readback(self.ctx, -1, slot, out.as_mut_ptr(), 0) };
+        self.check(st)?;
+        Ok((w as usize, h as usize, out))
+    }
+
+    /// Fence wait (src/main.rs:882-884).
+    pub fn sync(&mut self) -> Result<(), Error> {
+        let st = unsafe { rtce_sync(self.ctx) };
+        self.check(st)
+    }
+}
+
+impl Drop for ConeMarcher {
+    fn drop(&mut self) {
+        unsafe { rtce_destroy(self.ctx) }
+    }
+}
