@@ -181,7 +181,7 @@ def run_reference(args, wl):
     sample = f"{frames} of {wl['frames']} frames per step" + (", centred 256x144 window of every level" if rect else ", full image")
     line = {
         "impl": "reference", "metric": "Mrays/s (pixel-invocations of compute.glsl:main over all pyramid levels)",
-        "value": value, "unit": "Mrays/s", "n_gpus": 0, "steps": steps, "warmup": warmup,
+        "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
         "ms_per_step": tot_t / steps * 1e3 * (wl["frames"] / frames), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["name"], "levels": levels, "frames_per_step": wl["frames"]},
@@ -214,15 +214,33 @@ def run_ours(args, wl):
         raise SystemExit("bench.py: no CUDA device - the compute pass has no CPU fallback "
                          "(use --impl reference for the host-core baseline)")
     torch.cuda.set_device(local_rank)
+    # stdout carries ONE JSON line: native libraries (NCCL prints its version there) get stderr meanwhile
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n_gpus = world
 
+    # N > 1.  Frames are independent units (main.rs:291-316 renders each from its own push constants), so a
+    # frame-by-frame workload shards FRAMES: the camera path grows to frames x N, rank r traces frames
+    # [r*frames, (r+1)*frames) over the whole image into its own HBM, and there is no data-path collective
+    # (weak scaling).  An accumulating workload has one result image whose sum is order-defined, so it shards
+    # row bands of the final level instead (strong scaling) and gathers the one accumulated image per step.
+    weak = world > 1 and not wl["accumulate"]
+    frames_rank = wl["frames"]
+    if weak:
+        wl = dict(wl)
+        wl["frames"] = wl["frames"] * world
     spheres, rots, poss = workload_inputs(wl)
+    frames = wl["frames"]                                # of the whole job
+    if weak:
+        rots, poss = rots[rank * frames_rank:(rank + 1) * frames_rank], poss[rank * frames_rank:(rank + 1) * frames_rank]
+    else:
+        frames_rank = frames
     pcs = rt.make_push_constants(rots, poss)
-    frames = wl["frames"]
-    steps = args.steps if args.steps is not None else (200 if frames * wl["W"] * wl["H"] < 1e9 else 3)
+    steps = args.steps if args.steps is not None else (200 if frames_rank * wl["W"] * wl["H"] < 1e9 else 3)
     warmup = args.warmup if args.warmup is not None else (10 if steps >= 50 else 3)
     warmup = max(warmup, 3)
 
@@ -236,7 +254,7 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_GROUPS, args.groups)
     if args.strip_rows is not None:
         eng.set_option(rt.OPT_STRIP_ROWS, args.strip_rows)
-    slots = min(frames, 16)
+    slots = min(frames_rank, 16)
     eng.set_option(rt.OPT_FRAME_SLOTS, slots)
     if len(spheres) <= 8:
         eng.set_scene(scene.pack_mutable_data(objects=[(tuple(s[:3]), s[3]) for s in spheres]))
@@ -246,7 +264,7 @@ def run_ours(args, wl):
     levels = eng.levels
     Wf, Hf, _ = eng.level_info(-1, 0)
     y0, y1 = sharding.band_rows(Hf, world, rank)
-    if world > 1:
+    if world > 1 and not weak:
         eng.set_rect(0, y0, Wf, y1)
 
     def dev_final(nslots):
@@ -259,7 +277,6 @@ def run_ours(args, wl):
         if wl["accumulate"]:
             eng.trace_accumulate(pcs)
             if world > 1:
-                w_, h_, p = eng.lib, None, None
                 import ctypes as C
                 pw, ph, pp = C.c_int(), C.c_int(), C.c_void_p()
                 eng._check(eng.lib.rtce_accum_info(eng._ctx, C.byref(pw), C.byref(ph), C.byref(pp)), "rtce_accum_info")
@@ -267,21 +284,19 @@ def run_ours(args, wl):
                 return sharding.gather_bands(acc[:, y0:y1, :], Hf, dst=0)
         else:
             eng.trace(pcs)
-            if world > 1:
-                return sharding.gather_bands(dev_final(slots)[:, y0:y1, :], Hf, dst=0)
         return None
 
     # ---- work counters of one step (separate counted run; also the parity spot-check input) ----
     with torch.cuda.stream(stream):
         eng.set_option(rt.OPT_COUNTERS, 1)
         if wl["accumulate"]:
-            eng.trace_accumulate(pcs[: min(frames, slots)])
+            eng.trace_accumulate(pcs[: min(frames_rank, slots)])
         else:
-            eng.trace(pcs[: min(frames, slots)])
+            eng.trace(pcs[: min(frames_rank, slots)])
         cnt = eng.counters()
         cnt_last = eng.level_counters(-1)
         eng.set_option(rt.OPT_COUNTERS, 0)
-    scale = frames / min(frames, slots)   # static-pose workloads repeat the same frames
+    scale = frames_rank / min(frames_rank, slots)   # static-pose workloads repeat the same frames
     cnt_step = {k: int(cnt[k] * scale) for k in "RES"}
     cnt_last_step = {k: int(cnt_last[k] * scale) for k in "RES"}   # this rank's final-level launches
     if world > 1:
@@ -318,8 +333,11 @@ def run_ours(args, wl):
         launches_per_step = eng.counters()["launches"]
         # keep the GPU under the same load long enough for the sampler to see clocks (not timed)
         t_end = time.perf_counter() + (0.0 if args.profile else max(0.0, 1.0 - ms_total * 1e-3))
-        while time.perf_counter() < t_end:
-            step()
+        while time.perf_counter() < t_end:   # time-based, so no collective in here (ranks would diverge)
+            if wl["accumulate"]:
+                eng.trace_accumulate(pcs)
+            else:
+                eng.trace(pcs)
             torch.cuda.synchronize()
         clocks = sampler.stop()
     if world > 1:
@@ -357,7 +375,7 @@ def run_ours(args, wl):
     # ---- end to end through the public API with HOST buffers (push constants in, images out) ----
     e2e = None
     if not args.no_e2e:
-        band = y1 - y0
+        band = Hf if weak else y1 - y0
         if wl["accumulate"]:
             host = np.empty((Hf, Wf), dtype=np.float32)
             def e2e_step():
@@ -365,10 +383,10 @@ def run_ours(args, wl):
                 return eng.readback_accum()
             d2h = Wf * band * 4
         else:
-            pin = rt.PinnedBuffer((frames, Hf, Wf))
+            pin = rt.PinnedBuffer((frames_rank, Hf, Wf))
             def e2e_step():
                 eng.render_to_host(pcs, pin.array)
-            d2h = frames * Wf * band * 4
+            d2h = frames_rank * Wf * band * 4
         k_e2e = max(3, min(steps, int(2.0 / max(ms_step * 1e-3 * 8, 1e-4))))
         with torch.cuda.stream(stream):
             for _ in range(3):
@@ -390,7 +408,7 @@ def run_ours(args, wl):
                "h2d_bytes_per_step": int(pcs.nbytes) * world, "d2h_bytes_per_step": int(d2h), "steps": k_e2e,
                "note": "host PushConstantData in (passed by value into kernel parameters), every frame's final level "
                        "copied to pinned host memory (accumulate workloads: the one accumulated image); N>1: each rank "
-                       "returns its row band to the host"}
+                       "returns its own frames (accumulate workloads: its row band) to its host buffer"}
 
     if rank != 0:
         if world > 1:
@@ -454,18 +472,23 @@ def run_ours(args, wl):
     line = {
         "metric": "Mrays/s (pixel-invocations of compute.glsl:main over all pyramid levels)",
         "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": steps, "warmup": warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if n_gpus > 1 else "weak",
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if (n_gpus > 1 and not weak) else "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": wl["name"], "levels": levels, "frames_per_step": frames,
                    "rays_per_step": units_per_step, "primary_rays_per_step": Wf * Hf * frames,
                    "ms_per_frame": ms_step / frames,
-                   "parallelism": "1 GPU" if n_gpus == 1 else f"{n_gpus} row bands of the final level + one NCCL gather to rank 0 per step",
+                   "parallelism": "1 GPU" if n_gpus == 1 else
+                                  (f"frames sharded: {frames_rank} frames per rank x {n_gpus} ranks, whole image per frame, results stay in "
+                                   "each rank's HBM; no data-path collective (frames are independent units)" if weak else
+                                   f"{n_gpus} row bands of the final level + one NCCL gather of the accumulated image to rank 0 per step"),
                    "l2": f"no flush: each step rewrites {bytes_step / 1e6:.0f} MB of pyramid (> 126 MB L2 when frames >= 12 at 1080p); parents are meant to be L2 hits",
                    "kernel": {0: "auto (strip + fused coarse levels)", 1: "per-level", 2: "fused", 3: "strip + fused coarse levels"}[args.kernel]},
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps),
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps) * n_gpus,
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "mprimary_per_s": Wf * Hf * frames / (ms_step * 1e-3) / 1e6,
     }
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -144,8 +144,10 @@ struct OverflowParams {
 };
 cudaError_t launch_march_overflow(const OverflowParams& p, bool count, cudaStream_t st);
 
-// Accumulation extension: acc = (first ? 0 : acc) + img ; and the final scale by 1/frames.
-cudaError_t launch_accumulate(float* acc, const float* img, size_t n, bool first, cudaStream_t st);
+// Accumulation extension: acc = (...((first ? 0 : acc) + img[0]) + img[1]) ... + img[frames-1], the images
+// `slot_stride` floats apart, added in frame order in one pass; and the final scale by 1/frames.
+cudaError_t launch_accumulate(float* acc, const float* img, size_t slot_stride, int frames, size_t n, bool first,
+                              cudaStream_t st);
 cudaError_t launch_scale(float* acc, size_t n, float divisor, cudaStream_t st);
 
 }  // namespace rtce

@@ -137,10 +137,13 @@ cudaError_t launch_trace_level_large(const LevelParamsLarge& p, int frames, bool
 // ------------------------------------------------------------------------------------------
 // accumulation extension: running FP32 sum of final levels, scaled at the end
 // ------------------------------------------------------------------------------------------
-__global__ void k_accumulate(float* __restrict__ acc, const float* __restrict__ img, size_t n, int first) {
+__global__ void k_accumulate(float* __restrict__ acc, const float* __restrict__ img, size_t slot_stride, int frames,
+                             size_t n, int first) {
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        acc[i] = first ? img[i] : __fadd_rn(acc[i], img[i]);
+        float a = __fadd_rn(first ? 0.0f : acc[i], img[i]);
+        for (int f = 1; f < frames; f++) a = __fadd_rn(a, img[(size_t)f * slot_stride + i]);   // frame order
+        acc[i] = a;
     }
 }
 __global__ void k_scale(float* __restrict__ acc, size_t n, float divisor) {
@@ -149,9 +152,10 @@ __global__ void k_scale(float* __restrict__ acc, size_t n, float divisor) {
         acc[i] = __fdiv_rn(acc[i], divisor);
     }
 }
-cudaError_t launch_accumulate(float* acc, const float* img, size_t n, bool first, cudaStream_t st) {
-    if (!n) return cudaSuccess;
-    k_accumulate<<<148 * 8, 256, 0, st>>>(acc, img, n, first ? 1 : 0);
+cudaError_t launch_accumulate(float* acc, const float* img, size_t slot_stride, int frames, size_t n, bool first,
+                              cudaStream_t st) {
+    if (!n || frames <= 0) return cudaSuccess;
+    k_accumulate<<<148 * 8, 256, 0, st>>>(acc, img, slot_stride, frames, n, first ? 1 : 0);
     return cudaGetLastError();
 }
 cudaError_t launch_scale(float* acc, size_t n, float divisor, cudaStream_t st) {
