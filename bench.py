@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=None)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS))
+    ap.add_argument("--graph", type=int, default=None, help="RTCE_OPT_GRAPH: 1 = replay the launch chain from a CUDA graph (default), 0 = issue every launch")
     ap.add_argument("--frames", type=int, default=None, help="override frames per step (labelled in config)")
     ap.add_argument("--levels", type=int, default=None, help="override pyramid levels (configs[3] sweep)")
     ap.add_argument("--kernel", type=int, default=0, help="0 auto (= 3), 1 per-pixel kernel per level, 2 fused pyramid kernel, 3 strip kernels + fused coarse levels")
@@ -254,6 +255,8 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_GROUPS, args.groups)
     if args.strip_rows is not None:
         eng.set_option(rt.OPT_STRIP_ROWS, args.strip_rows)
+    if args.graph is not None:
+        eng.set_option(rt.OPT_GRAPH, args.graph)
     slots = min(frames_rank, 16)
     eng.set_option(rt.OPT_FRAME_SLOTS, slots)
     if len(spheres) <= 8:

@@ -94,9 +94,15 @@ typedef enum rtce_option {
                                    3 = strip kernel per large level + fused-pyramid kernel for the coarse levels */
     RTCE_OPT_STRIP_MIN_RAYS = 4,/* kernel plan 3: a level is traced by the strip kernel when it has at least this
                                    many rays per launch (level pixels x frames of the launch), default 400000 */
-    RTCE_OPT_COARSE_FUSED = 6,  /* kernel plan 3: 1 = the levels below the strip threshold in one fused-pyramid launch,
-                                   0 (default) = one latency-oriented per-pixel launch per level */
+    RTCE_OPT_COARSE_FUSED = 6,  /* kernel plan 3, the levels below the strip threshold: 0 (default) = one latency-oriented
+                                   per-pixel launch per level, 1 = one fused-pyramid launch, 2 = ONE launch in which a
+                                   thread-block cluster per frame walks the levels with a cluster barrier in between
+                                   (fewest launches; measured slower on B200 at 1080p: a frame is confined to 8 SMs) */
     RTCE_OPT_STRIP_ROWS = 7,    /* kernel plan 3: rows of a strip-kernel task (a task is 32 columns x this many rows), 1..32 */
+    RTCE_OPT_GRAPH = 8,         /* kernel plan 3: 1 (default) = the launch chain of a frame batch (every level of every group,
+                                   forks and joins included) is captured once into a CUDA graph and replayed by later
+                                   calls with the same batch shape; the per-call cameras travel through device memory.
+                                   0 = issue every launch.  Counters and the debug timelines always issue every launch. */
     RTCE_OPT_GROUPS = 5         /* kernel plan 3: number of frame groups (1..8, default 2) a batch is split into; every
                                    group runs its launch chain on its own stream so that latency-bound launches of one
                                    group overlap issue-bound launches of the others */

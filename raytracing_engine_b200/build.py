@@ -12,7 +12,7 @@ import subprocess
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "librtce.so")
-SOURCES = ["rtce_api.cu", "rtce_kernels.cu", "rtce_kernels_large.cu", "rtce_kernels_fused.cu", "rtce_kernels_strip.cu",
+SOURCES = ["rtce_api.cu", "rtce_kernels.cu", "rtce_kernels_large.cu", "rtce_kernels_fused.cu", "rtce_kernels_strip.cu", "rtce_kernels_coarse.cu",
            "rtce_measure.cu"]
 DEPS = ["rtce_api_trace.inc", "rtce_device.cuh", "rtce_march.cuh", "rtce_kernels.cuh", "rtce_host.hpp", "../../include/rtce.h"]
 
@@ -50,17 +50,20 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     env = dict(os.environ)
     env.pop("CC", None)   # the image exports CC/CXX wrappers that lack libgomp specs; use system g++
     env.pop("CXX", None)
-    cmd = [_nvcc(), *NVCC_FLAGS, "-ccbin", "/usr/bin/g++", "-o", LIB_PATH + ".tmp", *srcs]
+    # kernel-tuning experiments: extra -D flags / another output file (the shipped library uses neither)
+    extra = os.environ.get("RTCE_NVCC_EXTRA", "").split()
+    lib_out = os.environ.get("RTCE_LIB_OUT", LIB_PATH)
+    cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-ccbin", "/usr/bin/g++", "-o", lib_out + ".tmp", *srcs]
     out = subprocess.run(cmd, capture_output=True, text=True, env=env)
     log = out.stdout + out.stderr
     with open(os.path.join(PKG_DIR, "build_ptxas.log"), "w") as fh:
         fh.write(" ".join(cmd) + "\n" + log)
     if out.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + log[-6000:])
-    os.replace(LIB_PATH + ".tmp", LIB_PATH)
+    os.replace(lib_out + ".tmp", lib_out)
     if verbose:
         print(log)
-    return LIB_PATH
+    return lib_out
 
 
 if __name__ == "__main__":

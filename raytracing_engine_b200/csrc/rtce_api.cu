@@ -17,7 +17,7 @@
 using namespace rtce;
 
 static constexpr int kMaxGroups = 8;
-static constexpr unsigned kOverflowCap = 1u << 17;   // rays per frame group (9.4 MB each); beyond it long rays stay in their warp
+static constexpr unsigned kOverflowCap = 1u << 19;   // rays per frame group (38 MB each); beyond it long rays stay in their warp
 
 struct rtce_ctx {
     int device = 0;
@@ -28,7 +28,7 @@ struct rtce_ctx {
     cudaStream_t grp_stream[kMaxGroups] = {};   // one per frame group of a chunk, forked from / joined to `stream`
     cudaEvent_t ev_fork = nullptr, ev_join[kMaxGroups] = {};
     int groups = 2;                      // RTCE_OPT_GROUPS
-    bool coarse_fused = false;           // RTCE_OPT_COARSE_FUSED
+    int coarse_mode = 0;                 // RTCE_OPT_COARSE_FUSED: 0 one launch per level, 1 fused-pyramid kernel, 2 cluster kernel
     int strip_rows = 16;                 // RTCE_OPT_STRIP_ROWS
     // diagnostics (rtce_debug_launch_timeline): an event pair around every kernel launch
     struct LaunchMark { cudaEvent_t e0, e1; int kind, level, group; };
@@ -67,6 +67,18 @@ struct rtce_ctx {
     unsigned long long* d_counters = nullptr;
     unsigned long long* d_dbg = nullptr;   // strip-kernel warp timeline of one level (rtce_debug_strip_timeline)
     int dbg_level = -1;
+    // Cameras of the chunk being traced.  The strip and coarse-level kernels read them from device memory, not
+    // from their parameters: their launch chain is replayed from a CUDA graph whose parameters are frozen.
+    static constexpr int kCamRing = 8;
+    Cam* d_cams = nullptr;                 // [kMaxBatch]
+    Cam* h_cams = nullptr;                 // pinned staging, [kCamRing][kMaxBatch]
+    cudaEvent_t ev_cam[kCamRing] = {};     // staging entry consumed
+    unsigned cam_seq = 0;
+    // CUDA graphs of a chunk's launch chain (RTCE_OPT_GRAPH), valid while plan_version is unchanged
+    struct ChunkGraph { int frames, slot0; uint64_t version; cudaGraphExec_t exec; uint64_t launches; };
+    bool use_graph = true;
+    uint64_t plan_version = 1;             // bumped by every setter that changes what a launch chain looks like
+    std::vector<ChunkGraph> graphs;
     int* d_tickets = nullptr;    // [kMaxLevels][4] {task ticket, overflow count, overflow head, -} of the strip launches, zeroed per chunk
     float* d_oq = nullptr;       // overflow queue of the strip launches (kOverflowCap rays x 18 words), reused level after level
     uint64_t launches = 0;
@@ -113,6 +125,7 @@ int ensure_pyramid(rtce_ctx* c) {
     }
     cudaError_t e = cudaMalloc(&c->d_pyr, need * sizeof(float));
     if (e != cudaSuccess) return fail(c, RTCE_ERR_NOMEM, "cudaMalloc(pyramid)", e);
+    c->plan_version++;
     c->d_pyr_floats = need;
     c->slots_alloc = c->slots;
     // the reference clears every level image before its dispatch (main.rs:312); texels outside a
@@ -163,6 +176,8 @@ int rtce_create(int device, float render_dist, rtce_ctx** out) {
         cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaMalloc(&c->d_counters, 4 * kMaxLevels * sizeof(unsigned long long)) != cudaSuccess ||
         cudaMalloc(&c->d_tickets, sizeof(int) * kMaxGroups * kMaxLevels * 4) != cudaSuccess ||
+        cudaMalloc(&c->d_cams, sizeof(Cam) * kMaxBatch) != cudaSuccess ||
+        cudaMallocHost(&c->h_cams, sizeof(Cam) * kMaxBatch * rtce_ctx::kCamRing) != cudaSuccess ||
         cudaMalloc(&c->d_oq, sizeof(float) * kMaxGroups * (size_t)kOverflowCap * (10 + kSmallSceneMax)) != cudaSuccess) {
         rtce_destroy(c);
         return RTCE_ERR_CUDA;
@@ -171,6 +186,7 @@ int rtce_create(int device, float render_dist, rtce_ctx** out) {
         cudaEventCreateWithFlags(&c->ev_traced[i], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming);
     }
+    for (int i = 0; i < rtce_ctx::kCamRing; i++) cudaEventCreateWithFlags(&c->ev_cam[i], cudaEventDisableTiming);
     c->stream = c->own_stream;
     *out = c;
     return RTCE_OK;
@@ -186,6 +202,12 @@ void rtce_destroy(rtce_ctx* c) {
         if (c->ev_join[g]) cudaEventDestroy(c->ev_join[g]);
     }
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
+    c->graphs.clear();
+    for (int i = 0; i < rtce_ctx::kCamRing; i++)
+        if (c->ev_cam[i]) cudaEventDestroy(c->ev_cam[i]);
+    if (c->d_cams) cudaFree(c->d_cams);
+    if (c->h_cams) cudaFreeHost(c->h_cams);
     for (int i = 0; i < 2; i++) {
         if (c->ev_traced[i]) cudaEventDestroy(c->ev_traced[i]);
         if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
@@ -206,7 +228,9 @@ void rtce_destroy(rtce_ctx* c) {
 
 int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
     if (!c) return RTCE_ERR_INVALID;
+    c->plan_version++;
     switch (option) {
+        case RTCE_OPT_GRAPH: c->use_graph = value != 0; return RTCE_OK;
         case RTCE_OPT_COUNTERS: c->count = value != 0; return RTCE_OK;
         case RTCE_OPT_FRAME_SLOTS:
             if (value < 1 || value > 4096) return fail(c, RTCE_ERR_INVALID, "frame slots out of range");
@@ -225,7 +249,8 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             c->strip_rows = (int)value;
             return RTCE_OK;
         case RTCE_OPT_COARSE_FUSED:
-            c->coarse_fused = value != 0;
+            if (value < 0 || value > 2) return fail(c, RTCE_ERR_INVALID, "coarse plan out of range");
+            c->coarse_mode = (int)value;
             return RTCE_OK;
         case RTCE_OPT_GROUPS:
             if (value < 1 || value > kMaxGroups) return fail(c, RTCE_ERR_INVALID, "groups out of range");
@@ -243,6 +268,7 @@ int rtce_set_stream(rtce_ctx* c, void* cuda_stream) {
     if (!c) return RTCE_ERR_INVALID;
     DeviceGuard g(c->device);
     RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->plan_version++;
     c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
     return RTCE_OK;
 }
@@ -251,6 +277,7 @@ int rtce_set_spheres(rtce_ctx* c, const rtce_sphere* spheres, uint32_t n) {
     if (!c || (n && !spheres)) return fail(c, RTCE_ERR_INVALID, "rtce_set_spheres: null");
     if (n > RTCE_MAX_SPHERES) return fail(c, RTCE_ERR_LIMIT, "rtce_set_spheres: n > RTCE_MAX_SPHERES");
     DeviceGuard g(c->device);
+    c->plan_version++;
     c->n_spheres = (int)n;
     memset(c->small, 0, sizeof(c->small));
     if (n <= (uint32_t)kSmallSceneMax) {
@@ -319,6 +346,7 @@ int rtce_set_view(rtce_ctx* c, const rtce_constant_buffer* cb, int levels) {
         loff[i] = off;
         off += ((size_t)lw[i] * (size_t)lh[i] + 63) & ~(size_t)63;   // 256-byte aligned levels
     }
+    c->plan_version++;
     c->cb = *cb;
     c->levels = levels;
     memcpy(c->lw, lw, sizeof(lw));
@@ -343,6 +371,7 @@ int rtce_set_rect(rtce_ctx* c, int x0, int y0, int x1, int y1) {
     if (!c) return RTCE_ERR_INVALID;
     if (!c->have_view) return fail(c, RTCE_ERR_STATE, "rtce_set_rect: view not set");
     const int W = c->lw[c->levels - 1], H = c->lh[c->levels - 1];
+    c->plan_version++;
     if (x0 == 0 && y0 == 0 && x1 == 0 && y1 == 0) {
         c->rect[0] = c->rect[1] = c->rect[2] = c->rect[3] = 0;
         return RTCE_OK;

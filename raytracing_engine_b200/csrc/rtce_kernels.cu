@@ -147,7 +147,13 @@ __global__ void __launch_bounds__(256)
     const int f = blockIdx.z;
     unsigned cR = 0, cE = 0, cS = 0;
     if (x < P.x1 && y < P.y1) {
-        const Cam& cam = P.cam[f];
+        Cam cam;
+        {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(P.cams + f));
+            const float4 t = __ldg(reinterpret_cast<const float4*>(P.cams + f) + 1);
+            cam.rot[0] = q.x; cam.rot[1] = q.y; cam.rot[2] = q.z; cam.rot[3] = q.w;
+            cam.pos[0] = t.x; cam.pos[1] = t.y; cam.pos[2] = t.z; cam.pad = 0.0f;
+        }
         const float4 col = col_terms(cam, norm_coord(x, P.isx, P.ratx));
         const float4 row = row_terms(cam, norm_coord(y, P.isy, P.raty));
         float start = 1.0f;   // compute.glsl:79
@@ -157,7 +163,7 @@ __global__ void __launch_bounds__(256)
         float len = 0.0f;
         bool go = first_step<N, COUNT>(ray, len, P.threshold, P.render_dist, cE, cS);
         float last = len;
-        while (go) go = march_step_pred<N, COUNT>(ray, len, last, P.threshold, P.render_dist, P.sph, cE, cS);
+        while (go) go = march_block_pred<N, COUNT, RTCE_PRED_BLOCK>(ray, len, last, P.threshold, P.render_dist, P.sph, cE, cS);
         P.out[(size_t)f * P.slot_stride + (size_t)y * (size_t)P.w + (size_t)x] = glsl_max(fadd(start, len), 0.0f);   // :84, :86
         cR = 1;
     }

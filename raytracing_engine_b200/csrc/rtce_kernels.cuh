@@ -34,6 +34,8 @@ struct LevelParams {
     float threshold;         // 1.4142135 * 8 * imageSize.x  (compute.glsl:75)
     float render_dist;
     float4 sph[kSmallSceneMax];   // {pos.xyz, size}
+    const Cam* cams;         // the same cameras in device memory (k_trace_level_pix reads these: launches that
+                             // are replayed from a CUDA graph cannot carry per-step values in their parameters)
     Cam cam[kMaxBatch];
 };
 
@@ -88,12 +90,20 @@ struct FusedParams {
     float ratx, raty, render_dist;
     FusedLevel lv[kMaxLevels];
     float4 sph[kSmallSceneMax];
+    const Cam* cams;          // the cameras in device memory (cluster kernel; the fused kernel reads cam[])
     Cam cam[kMaxBatch];
 };
 // Returns cudaErrorNotSupported when the geometry does not fit the kernel's shared-memory regions
 // (the caller then uses the per-level kernels).
 bool fused_geometry_ok(const FusedParams& p);
 cudaError_t launch_trace_fused(const FusedParams& p, int frames, bool count, cudaStream_t st);
+
+// ---- cluster kernel (objCount <= 8): the coarse levels [0, p.levels) of a frame batch in ONE launch ----
+// One thread-block cluster (1..8 CTAs of kCoarseThreads) per frame walks the levels with a cluster
+// barrier in between; FusedParams describes the level prefix (fill as for the fused kernel, plus
+// `cams`; gx0 / gy0 / ntx / nty and cam[] are not used).  Requires RENDER_DIST > 0.
+constexpr int kCoarseThreads = 512;
+cudaError_t launch_trace_coarse(const FusedParams& p, int frames, bool count, cudaStream_t st);
 
 // ---- strip kernel (objCount <= 8): ONE level of a frame batch, persistent warps ---------------
 // The levels that hold almost all rays (the last three: 75 % + 19 % + 5 %) are each traced by one
@@ -123,7 +133,7 @@ struct StripParams {
     int n_spheres;
     float isx, isy, ratx, raty, threshold, render_dist;
     float4 sph[kSmallSceneMax];
-    Cam cam[kMaxBatch];
+    const Cam* cams;          // cameras of the `frames` frames, device memory, 32-byte records
 };
 cudaError_t launch_trace_strip(const StripParams& p, bool count, cudaStream_t st);
 

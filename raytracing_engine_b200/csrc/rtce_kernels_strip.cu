@@ -28,7 +28,16 @@ namespace rtce {
 constexpr int kQCap = 64;          // queue entries per warp: < 32 parked + <= 32 pushed by one row
 constexpr int kRefillMin = 8;      // refill when this many lanes are idle
 constexpr int kPinWords = 40;       // per-warp scratch for pinning uniforms (>= 2 + 4 * 8, multiple of 4)
-constexpr int kMaxAge = 6;         // tail trips after which a ray is evicted to the overflow queue
+#ifndef RTCE_MAX_AGE
+#define RTCE_MAX_AGE 3
+#endif
+#ifndef RTCE_TAIL_BUDGET
+#define RTCE_TAIL_BUDGET (1 << 30)
+#endif
+constexpr int kMaxAge = RTCE_MAX_AGE;   // tail trips after which a ray is evicted to the overflow queue
+constexpr int kTailBudget = RTCE_TAIL_BUDGET;   // tail trips a warp spends on ONE task before it evicts every tail ray it
+                                                // holds: a tile whose rays all need ~6 trips would otherwise keep one
+                                                // warp busy for 30+ us after the others have run out of tasks
 constexpr int kEvictMin = 8;       // evict in groups of at least this many rays (or when the local queue is empty)
 constexpr int kLeaveBelow = 16;    // with the queue empty, park the stragglers below this many active lanes
 #define RTCE_SQ_WORDS(N) (10 + (N))   // o(3) s(3) len last start offset d[N]
@@ -105,8 +114,8 @@ RTCE_DEV void oq_load(const float* buf, unsigned cap, unsigned k, Ray<N>& r, flo
 // after this kernel (k_march_overflow), instead of serialising in this warp.
 template <int N, bool COUNT>
 RTCE_DEV int tail_march(float* q, int qn, const bool drain, float* __restrict__ img, const float thr, const float rd,
-                        const float4* __restrict__ sph, const OverflowQueue& oq, bool& oq_open, unsigned& cE, unsigned& cS,
-                        const int lane) {
+                        const float4* __restrict__ sph, const OverflowQueue& oq, bool& oq_open, int& budget, unsigned& cE,
+                        unsigned& cS, const int lane) {
     const unsigned lt = (1u << lane) - 1u;
     bool active = false;
     Ray<N> r;
@@ -116,9 +125,10 @@ RTCE_DEV int tail_march(float* q, int qn, const bool drain, float* __restrict__ 
     for (;;) {
         unsigned am = __ballot_sync(RTCE_FULL, active);
         if (oq_open) {
-            const bool old = active && age >= kMaxAge;
+            const bool spent = budget <= 0;
+            const bool old = active && (age >= kMaxAge || spent);
             const unsigned om = __ballot_sync(RTCE_FULL, old);
-            if (om != 0u && (__popc(om) >= kEvictMin || qn == 0)) {
+            if (om != 0u && (__popc(om) >= kEvictMin || qn == 0 || spent)) {
                 const int n = __popc(om);
                 unsigned base = 0;
                 if (lane == __ffs(om) - 1) base = atomicAdd(oq.count, (unsigned)n);
@@ -160,11 +170,15 @@ RTCE_DEV int tail_march(float* q, int qn, const bool drain, float* __restrict__ 
                 active = false;
             }
         }
+        budget--;
     }
     return qn;
 }
 
 // The overflow queue of one strip launch, marched to the end by every warp of the device.
+#ifndef RTCE_OQ_PER_WARP
+#define RTCE_OQ_PER_WARP 32
+#endif
 template <int N, bool COUNT>
 __global__ void __launch_bounds__(128)
     k_march_overflow(const __grid_constant__ OverflowParams P) {
@@ -174,7 +188,7 @@ __global__ void __launch_bounds__(128)
     // Warps in use grow with the queue (~48 rays each, refilled as rays finish): a short queue is
     // bound by the dependent chain of its longest ray and runs fastest with one warp per
     // scheduler; a long one is issue-bound and wants them all.
-    if ((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * 48u >= n) return;
+    if ((blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * (unsigned)RTCE_OQ_PER_WARP >= n) return;
     float4 sph[N > 0 ? N : 1];
 #pragma unroll
     for (int i = 0; i < N; i++) sph[i] = P.sph[i];
@@ -204,7 +218,7 @@ __global__ void __launch_bounds__(128)
         }
         if (active) {
             unsigned e = 0, s = 0;
-            const bool go = march_step_pred<N, COUNT>(r, len, last, thr, rd, sph, e, s);
+            const bool go = march_block_pred<N, COUNT, RTCE_PRED_BLOCK>(r, len, last, thr, rd, sph, e, s);
             if (COUNT) { cE += e; cS += s; }
             if (!go) {
                 img[off] = glsl_max(fadd(start, len), 0.0f);   // compute.glsl:84, :86
@@ -336,13 +350,10 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
             if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
         }
         ndone++;
+        int budget = kTailBudget;   // of this task
         Cam cam;
         {
-            const Cam& c0 = P.cam[f];
-#pragma unroll
-            for (int i = 0; i < 4; i++) pin[i] = c0.rot[i];
-#pragma unroll
-            for (int i = 0; i < 3; i++) pin[4 + i] = c0.pos[i];
+            if (lane < 8) pin[lane] = __ldg(reinterpret_cast<const float*>(P.cams + f) + lane);
             __syncwarp();
 #pragma unroll
             for (int i = 0; i < 4; i++) cam.rot[i] = pin[i];
@@ -379,7 +390,7 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
                     if (cont2) sq_push<N>(q, qn + __popc(m2 & lt), ray, len, last, start, (unsigned)(op - img));
                     qn += __popc(m2);
                     __syncwarp();
-                    if (qn >= 32) qn = tail_march<N, COUNT>(q, qn, false, img, thr, rd, sph, oq, oq_open, cE, cS, lane);
+                    if (qn >= 32) qn = tail_march<N, COUNT>(q, qn, false, img, thr, rd, sph, oq, oq_open, budget, cE, cS, lane);
                 }
             }
             if (HAS_PARENT) {
@@ -392,7 +403,8 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
         ticket = __shfl_sync(RTCE_FULL, next, 0);
     }
     if (P.dbg) t1 = globaltimer_ns();
-    if (qn > 0) qn = tail_march<N, COUNT>(q, qn, true, img, thr, rd, sph, oq, oq_open, cE, cS, lane);
+    int budget = kTailBudget;
+    if (qn > 0) qn = tail_march<N, COUNT>(q, qn, true, img, thr, rd, sph, oq, oq_open, budget, cE, cS, lane);
     if (P.dbg && lane == 0) {
         unsigned long long* d = P.dbg + 4 * (size_t)(blockIdx.x * (kStripThreads / 32) + warp);
         d[0] = t0; d[1] = t1; d[2] = globaltimer_ns(); d[3] = (unsigned long long)ndone;

@@ -262,4 +262,48 @@ RTCE_DEV bool march_step_pred(Ray<N>& r, float& len, float& last, const float th
     return len < rd;               // :44
 }
 
+// K branch-free trips in a row for the latency-bound marchers.  A single warp per scheduler pays
+// ~150 cycles of loop control (votes, convergence barriers, branches) around a ~200-cycle trip;
+// here the control is paid once per K trips.  A lane whose ray ends inside the block keeps its
+// final state (every later trip of the block is computed and discarded), so the values are those
+// of march_step.  Returns true while the ray is still going.
+#ifndef RTCE_PRED_BLOCK
+#define RTCE_PRED_BLOCK 4
+#endif
+template <int N, bool COUNT, int K>
+RTCE_DEV bool march_block_pred(Ray<N>& r, float& len, float& last, const float threshold, const float rd,
+                               const float4* __restrict__ sph, unsigned& cE, unsigned& cS) {
+    bool go = true;
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        const float px = fadd(r.ox, fmul(r.sx, len));   // :45
+        const float py = fadd(r.oy, fmul(r.sy, len));
+        const float pz = fadd(r.oz, fmul(r.sz, len));
+        float dist = rd;                                           // :49
+        const float radius = fmul(fadd(len, 1.0f), threshold);    // :50
+        float dn[N > 0 ? N : 1];
+#pragma unroll
+        for (int i = 0; i < N; i++) {   // :51-57
+            const float dx = fsub(px, sph[i].x), dy = fsub(py, sph[i].y), dz = fsub(pz, sph[i].z);
+            const float exact = fsub(sqrt_fast(fadd(fadd(fmul(dx, dx), fmul(dy, dy)), fmul(dz, dz))), sph[i].w);
+            const float bound = fsub(r.d[i], last);
+            const bool refresh = bound <= radius;
+            if (COUNT) cE += (go && refresh) ? 1u : 0u;
+            dn[i] = refresh ? exact : bound;
+            dist = glsl_min(dist, dn[i]);
+        }
+        if (COUNT) cS += go ? 1u : 0u;
+        const float last_n = glsl_max(dist, 0.0f);   // :59
+        const float len_a = fadd(len, last_n);       // :60
+        const bool hit = dist <= radius;             // :62-65
+        const float len_n = hit ? fsub(len_a, radius) : len_a;
+#pragma unroll
+        for (int i = 0; i < N; i++) r.d[i] = go ? dn[i] : r.d[i];
+        last = go ? last_n : last;
+        len = go ? len_n : len;
+        go = go && !hit && len_n < rd;               // :44
+    }
+    return go;
+}
+
 }  // namespace rtce

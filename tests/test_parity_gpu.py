@@ -17,15 +17,19 @@ pytestmark = pytest.mark.gpu
 
 # (kernel plan, strip threshold): per-pixel kernels; fused pyramid; strip kernel on EVERY level (threshold 0,
 # level 0 included); strip kernel on the larger levels over a fused-pyramid prefix; the shipped default
+# third element: plan of the coarse levels below the strip threshold (0 one launch per level = default, 1 fused, 2 cluster kernel)
 MODES = [(rt.KERNEL_PER_LEVEL, None), (rt.KERNEL_FUSED, None), (rt.KERNEL_STRIP, 0), (rt.KERNEL_STRIP, 3000),
-         (rt.KERNEL_AUTO, None)]
+         (rt.KERNEL_STRIP, 3000, 1), (rt.KERNEL_STRIP, 3000, 2), (rt.KERNEL_STRIP, 10**9, 2), (rt.KERNEL_AUTO, None)]
 
 
 def _set_mode(e, mode):
-    kernel, min_rays = mode if isinstance(mode, tuple) else (mode, None)
+    mode = mode if isinstance(mode, tuple) else (mode, None)
+    kernel, min_rays = mode[0], mode[1]
     e.set_option(rt.OPT_KERNEL, kernel)
     if min_rays is not None:
         e.set_option(rt.OPT_STRIP_MIN_RAYS, min_rays)
+    if len(mode) > 2:
+        e.set_option(rt.OPT_COARSE_FUSED, mode[2])
 
 
 def _bits(a):
@@ -182,6 +186,48 @@ def test_render_to_host_and_accumulate(case_table):
         st = rt.make_push_constants(*camera.static_path(2))
         e.trace_accumulate(st)
         assert np.array_equal(_bits(e.readback_accum()), _bits(singles[0]))
+
+
+@pytest.mark.parametrize("groups", [1, 2, 4, 8])
+def test_graph_replay_equals_issued_launches(groups, case_table):
+    """RTCE_OPT_GRAPH: a captured launch chain replayed with NEW cameras (they travel through device memory),
+    after a scene change (graph invalidated) and for a ragged last chunk == every launch issued == the checker."""
+    o = oracle.best()
+    case = case_table["default_800x600"]
+    sph = case[2]
+    rots, poss = camera.bench_camera_path(22)
+    pcs = rt.make_push_constants(rots, poss)
+
+    def run(graph, pcs_, spheres=None):
+        with _engine(case, (rt.KERNEL_STRIP, 3000), slots=8) as e:
+            e.set_option(rt.OPT_GROUPS, groups)
+            e.set_option(rt.OPT_GRAPH, graph)
+            e.trace(pcs_[:8])                       # graph path: capture + first replay target
+            a = [e.readback(-1, k) for k in range(8)]
+            e.trace(pcs_[8:16])                     # replay, other cameras
+            b = [[e.readback(i, k) for i in range(e.levels)] for k in range(8)]
+            if spheres is not None:
+                e.set_spheres(spheres)              # frozen scene parameters must not survive this
+            e.trace(pcs_[11:22])                    # chunks of 8 + 3: second shape
+            c = [e.readback(-1, k) for k in range(3)]
+            return a, b, c
+
+    moved = np.array(sph, np.float32).copy()
+    moved[:, 0] += 0.75
+    ga, gb, gc = run(1, pcs, moved)
+    ia, ib, ic = run(0, pcs, moved)
+    for k in range(8):
+        assert np.array_equal(_bits(ga[k]), _bits(ia[k])), k
+        for i in range(len(gb[k])):
+            assert np.array_equal(_bits(gb[k][i]), _bits(ib[k][i])), (k, i)
+    for k in range(3):
+        assert np.array_equal(_bits(gc[k]), _bits(ic[k])), k
+    W, H = case[3], case[4]
+    ref, _ = o.trace(sph, [W, H], scene.view_ratio(W, H), rots[13], poss[13], 1000.0, case[5])
+    for i, r in enumerate(ref):
+        assert np.array_equal(_bits(gb[5][i]), _bits(r)), i
+    ref, _ = o.trace(moved, [W, H], scene.view_ratio(W, H), rots[20], poss[20], 1000.0, case[5])
+    assert np.array_equal(_bits(gc[1]), _bits(ref[-1]))
 
 
 def test_large_scene_kernel_matches_checker():

@@ -22,7 +22,7 @@ with rt.Engine(0, 1000.0) as e:
     e.launch_timeline(fetch=False)
     e.trace(pcs)
     t = e.launch_timeline()
-    names = {0: "perpixel", 1: "strip", 2: "overflow", 3: "pix", 10: "fused"}
+    names = {0: "perpixel", 1: "strip", 2: "overflow", 3: "pix", 4: "cluster", 10: "fused"}
     print(f"groups={groups} min_rays={min_rays}: {len(t)} launches, span {t[:, 1].max() * 1e3:.1f} us")
     for r in t:
         print(f"  g{int(r[4]):2d} {names[int(r[2])]:9s} L{int(r[3])}  {r[0] * 1e3:8.1f} -> {r[1] * 1e3:8.1f}  ({(r[1] - r[0]) * 1e3:7.1f} us)")

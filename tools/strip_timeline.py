@@ -6,11 +6,13 @@ import raytracing_engine_b200 as rt
 from raytracing_engine_b200 import camera, scene
 
 level = int(sys.argv[1]) if len(sys.argv) > 1 else -1
+groups = int(sys.argv[2]) if len(sys.argv) > 2 else 1
 frames = 16
 rots, poss = camera.bench_camera_path(frames)
 pcs = rt.make_push_constants(rots, poss)
 with rt.Engine(0, 1000.0) as e:
     e.set_option(rt.OPT_FRAME_SLOTS, frames)
+    e.set_option(rt.OPT_GROUPS, groups)
     e.set_scene(scene.default_mutable_data())
     e.set_view(1920, 1080)
     for _ in range(3):
