@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=None)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS))
+    ap.add_argument("--in-flight", type=int, default=None,
+                    help="RTCE_OPT_FRAMES_IN_FLIGHT for frame-by-frame workloads (default 4): batches of consecutive steps "
+                         "rotate over this many windows of frame slots and overlap on the device; 1 = strict stream order")
     ap.add_argument("--graph", type=int, default=None, help="RTCE_OPT_GRAPH: 1 = replay the launch chain from a CUDA graph (default), 0 = issue every launch")
     ap.add_argument("--frames", type=int, default=None, help="override frames per step (labelled in config)")
     ap.add_argument("--levels", type=int, default=None, help="override pyramid levels (configs[3] sweep)")
@@ -225,20 +228,19 @@ def run_ours(args, wl):
     n_gpus = world
 
     # N > 1.  Frames are independent units (main.rs:291-316 renders each from its own push constants), so a
-    # frame-by-frame workload shards FRAMES: the camera path grows to frames x N, rank r traces frames
-    # [r*frames, (r+1)*frames) over the whole image into its own HBM, and there is no data-path collective
-    # (weak scaling).  An accumulating workload has one result image whose sum is order-defined, so it shards
-    # row bands of the final level instead (strong scaling) and gathers the one accumulated image per step.
+    # frame-by-frame workload shards FRAMES: the job is N batches of the workload's shape, rank r traces batch r
+    # (the same seeded poses on every rank, so that the work per GPU is exactly fixed) over the whole image
+    # into its own HBM, and there is no data-path collective (weak scaling).  An accumulating workload has one
+    # result image whose sum is order-defined, so it shards row bands of the final level instead (strong
+    # scaling) and gathers the one accumulated image per step.
     weak = world > 1 and not wl["accumulate"]
     frames_rank = wl["frames"]
+    spheres, rots, poss = workload_inputs(wl)            # this rank's batch
     if weak:
         wl = dict(wl)
         wl["frames"] = wl["frames"] * world
-    spheres, rots, poss = workload_inputs(wl)
     frames = wl["frames"]                                # of the whole job
-    if weak:
-        rots, poss = rots[rank * frames_rank:(rank + 1) * frames_rank], poss[rank * frames_rank:(rank + 1) * frames_rank]
-    else:
+    if not weak:
         frames_rank = frames
     pcs = rt.make_push_constants(rots, poss)
     steps = args.steps if args.steps is not None else (200 if frames_rank * wl["W"] * wl["H"] < 1e9 else 3)
@@ -257,6 +259,8 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_STRIP_ROWS, args.strip_rows)
     if args.graph is not None:
         eng.set_option(rt.OPT_GRAPH, args.graph)
+    in_flight = 1 if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 4)
+    eng.set_option(rt.OPT_FRAMES_IN_FLIGHT, in_flight)
     slots = min(frames_rank, 16)
     eng.set_option(rt.OPT_FRAME_SLOTS, slots)
     if len(spheres) <= 8:
@@ -330,6 +334,7 @@ def run_ours(args, wl):
         e0.record(stream)
         for _ in range(steps):
             step()
+        eng.flush()   # frames in flight: the end event comes after every batch
         e1.record(stream)
         barrier()
         ms_total = e0.elapsed_time(e1)
@@ -366,7 +371,7 @@ def run_ours(args, wl):
                 step()
             tl = eng.launch_timeline(max_launches=4096)
             eng.launch_timeline(max_launches=0)   # disarm
-            eng.set_option(rt.OPT_GROUPS, args.groups if args.groups is not None else 2)
+            eng.set_option(rt.OPT_GROUPS, args.groups if args.groups is not None else 0)
             barrier()
         sel = tl[(tl[:, 2] == 1) & (tl[:, 3] == levels - 1)]
         if len(sel):
@@ -481,9 +486,11 @@ def run_ours(args, wl):
                    "rays_per_step": units_per_step, "primary_rays_per_step": Wf * Hf * frames,
                    "ms_per_frame": ms_step / frames,
                    "parallelism": "1 GPU" if n_gpus == 1 else
-                                  (f"frames sharded: {frames_rank} frames per rank x {n_gpus} ranks, whole image per frame, results stay in "
-                                   "each rank's HBM; no data-path collective (frames are independent units)" if weak else
+                                  (f"frames sharded: {n_gpus} batches of {frames_rank} frames, one per rank (the same seeded poses on every rank: "
+                                   "fixed work per GPU), whole image per frame, results stay in each rank's HBM; no data-path "
+                                   "collective (frames are independent units)" if weak else
                                    f"{n_gpus} row bands of the final level + one NCCL gather of the accumulated image to rank 0 per step"),
+                   "frames_in_flight": in_flight if not wl["accumulate"] else "3 chunks (internal to rtce_trace_accumulate)",
                    "l2": f"no flush: each step rewrites {bytes_step / 1e6:.0f} MB of pyramid (> 126 MB L2 when frames >= 12 at 1080p); parents are meant to be L2 hits",
                    "kernel": {0: "auto (strip + fused coarse levels)", 1: "per-level", 2: "fused", 3: "strip + fused coarse levels"}[args.kernel]},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps) * n_gpus,

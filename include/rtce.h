@@ -99,13 +99,23 @@ typedef enum rtce_option {
                                    thread-block cluster per frame walks the levels with a cluster barrier in between
                                    (fewest launches; measured slower on B200 at 1080p: a frame is confined to 8 SMs) */
     RTCE_OPT_STRIP_ROWS = 7,    /* kernel plan 3: rows of a strip-kernel task (a task is 32 columns x this many rows), 1..32 */
+    RTCE_OPT_FRAMES_IN_FLIGHT = 9, /* 1..4, default 1.  The reference keeps frames in flight behind its swapchain
+                                   (main.rs:859-884: acquire, submit, fence of the PREVIOUS frame).  With W > 1 successive
+                                   rtce_trace_batch calls rotate over W windows of frame slots, each with its own streams:
+                                   a call starts after everything enqueued on the context's stream so far, but NOT after
+                                   the W-1 calls before it, so the latency-bound levels of one batch run under the
+                                   issue-bound final level of another.  The context's stream is only ordered after the
+                                   batch whose window the next call reuses; rtce_flush (stream-level) or rtce_sync /
+                                   rtce_readback* (host-level) order it after everything.  rtce_level_info and
+                                   rtce_readback address the window of the latest call.  W = 1 is strict stream order. */
     RTCE_OPT_GRAPH = 8,         /* kernel plan 3: 1 (default) = the launch chain of a frame batch (every level of every group,
                                    forks and joins included) is captured once into a CUDA graph and replayed by later
                                    calls with the same batch shape; the per-call cameras travel through device memory.
                                    0 = issue every launch.  Counters and the debug timelines always issue every launch. */
-    RTCE_OPT_GROUPS = 5         /* kernel plan 3: number of frame groups (1..8, default 2) a batch is split into; every
-                                   group runs its launch chain on its own stream so that latency-bound launches of one
-                                   group overlap issue-bound launches of the others */
+    RTCE_OPT_GROUPS = 5         /* kernel plan 3: number of frame groups (1..8) a batch is split into; every group runs its
+                                   launch chain on its own stream so that latency-bound launches of one group overlap
+                                   issue-bound launches of the others.  0 (default) = auto: 2 in strict stream order,
+                                   1 when frames are in flight on several lanes (those already overlap) */
 } rtce_option;
 
 /* -- lifetime ------------------------------------------------------------------------------
@@ -150,7 +160,9 @@ int rtce_host_image_size(int levels, int level, float view_w, float view_h, floa
 int rtce_trace(rtce_ctx* ctx, const rtce_push_constants* pc);
 int rtce_trace_batch(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
 /* Extension ("progressive accumulation"): trace `frames` frames and keep only the
- * running FP32 sum of their final levels, divided by `frames` at the end, in an internal image. */
+ * running FP32 sum of their final levels, divided by `frames` at the end, in an internal image.
+ * Up to three chunks of frames are traced side by side (own streams, own windows of slots); the sum
+ * is taken on the context's stream in frame order. */
 int rtce_trace_accumulate(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
 int rtce_accum_info(const rtce_ctx* ctx, int* w, int* h, float** device_ptr);
 
@@ -166,6 +178,9 @@ int rtce_render_to_host(rtce_ctx* ctx, const rtce_push_constants* pcs, int frame
 int rtce_host_alloc(void** out, size_t nbytes);
 int rtce_host_free(void* p);
 int rtce_sync(rtce_ctx* ctx);                        /* fence wait, main.rs:882-884 */
+/* Make the context's stream wait (on the device, the host does not block) for every batch traced so far:
+ * after it, work enqueued on the context's stream sees all images.  A no-op with one frame in flight. */
+int rtce_flush(rtce_ctx* ctx);
 int rtce_get_counters(rtce_ctx* ctx, rtce_counters* out);
 /* The same per pyramid level (negative = from the last).  A fused-pyramid launch books all the levels it
  * traces under its finest one. */

@@ -19,15 +19,41 @@ using namespace rtce;
 static constexpr int kMaxGroups = 8;
 static constexpr unsigned kOverflowCap = 1u << 19;   // rays per frame group (38 MB each); beyond it long rays stay in their warp
 
+// A lane is one self-contained launch chain: its own stream (plus one per frame group), its own
+// window of frame slots in the pyramid allocation, task counters, overflow queues, camera buffer
+// and captured graphs.  Lane 0 is the context's classic path.  With RTCE_OPT_FRAMES_IN_FLIGHT > 1
+// successive rtce_trace_batch calls rotate over the lanes and overlap on the device — the
+// latency-bound coarse levels and long-ray launches of one batch run under the issue-bound final
+// level of another — and rtce_trace_accumulate rotates its chunks the same way.
+static constexpr int kMaxLanes = 4;
+static constexpr int kCamRing = 8;
+struct ChunkGraph { int frames, slot0; bool own_stream; uint64_t version; cudaGraphExec_t exec; uint64_t launches; };
+struct Lane {
+    bool ready = false;
+    bool pending = false;                  // traced since the context's stream last waited for it
+    cudaStream_t st = nullptr;             // the lane's chain when it does not run on the context's stream
+    cudaStream_t grp_stream[kMaxGroups] = {};   // one per frame group of a chunk, forked from / joined to the chain's stream
+    cudaEvent_t ev_fork = nullptr, ev_join[kMaxGroups] = {};
+    cudaEvent_t ev_done = nullptr;         // last chunk traced
+    cudaEvent_t ev_free = nullptr;         // the consumer is done with the window
+    // Cameras of the chunk being traced.  The strip and coarse-level kernels read them from device memory, not
+    // from their parameters: their launch chain is replayed from a CUDA graph whose parameters are frozen.
+    Cam* d_cams = nullptr;                 // [kMaxBatch]
+    Cam* h_cams = nullptr;                 // pinned staging, [kCamRing][kMaxBatch]
+    cudaEvent_t ev_cam[kCamRing] = {};     // staging entry consumed
+    unsigned cam_seq = 0;
+    std::vector<ChunkGraph> graphs;
+    int* d_tickets = nullptr;    // [kMaxGroups][kMaxLevels][4] {task ticket, overflow count, overflow head, -}, zeroed per chunk
+    float* d_oq = nullptr;       // overflow queues of the strip launches (kMaxGroups x kOverflowCap rays x 18 words)
+};
+
 struct rtce_ctx {
     int device = 0;
     float render_dist = 1000.0f;
     cudaStream_t own_stream = nullptr;   // created by rtce_create
     cudaStream_t stream = nullptr;       // the stream work is issued on (own_stream or the caller's)
     cudaStream_t copy_stream = nullptr;  // D2H copies of rtce_render_to_host
-    cudaStream_t grp_stream[kMaxGroups] = {};   // one per frame group of a chunk, forked from / joined to `stream`
-    cudaEvent_t ev_fork = nullptr, ev_join[kMaxGroups] = {};
-    int groups = 2;                      // RTCE_OPT_GROUPS
+    int groups = 0;                      // RTCE_OPT_GROUPS (0 = auto)
     int coarse_mode = 0;                 // RTCE_OPT_COARSE_FUSED: 0 one launch per level, 1 fused-pyramid kernel, 2 cluster kernel
     int strip_rows = 16;                 // RTCE_OPT_STRIP_ROWS
     // diagnostics (rtce_debug_launch_timeline): an event pair around every kernel launch
@@ -67,20 +93,15 @@ struct rtce_ctx {
     unsigned long long* d_counters = nullptr;
     unsigned long long* d_dbg = nullptr;   // strip-kernel warp timeline of one level (rtce_debug_strip_timeline)
     int dbg_level = -1;
-    // Cameras of the chunk being traced.  The strip and coarse-level kernels read them from device memory, not
-    // from their parameters: their launch chain is replayed from a CUDA graph whose parameters are frozen.
-    static constexpr int kCamRing = 8;
-    Cam* d_cams = nullptr;                 // [kMaxBatch]
-    Cam* h_cams = nullptr;                 // pinned staging, [kCamRing][kMaxBatch]
-    cudaEvent_t ev_cam[kCamRing] = {};     // staging entry consumed
-    unsigned cam_seq = 0;
     // CUDA graphs of a chunk's launch chain (RTCE_OPT_GRAPH), valid while plan_version is unchanged
-    struct ChunkGraph { int frames, slot0; uint64_t version; cudaGraphExec_t exec; uint64_t launches; };
     bool use_graph = true;
     uint64_t plan_version = 1;             // bumped by every setter that changes what a launch chain looks like
-    std::vector<ChunkGraph> graphs;
-    int* d_tickets = nullptr;    // [kMaxLevels][4] {task ticket, overflow count, overflow head, -} of the strip launches, zeroed per chunk
-    float* d_oq = nullptr;       // overflow queue of the strip launches (kOverflowCap rays x 18 words), reused level after level
+    // lanes: independent launch chains over their own window of frame slots (see Lane)
+    Lane lanes[kMaxLanes];
+    int in_flight = 1;                     // RTCE_OPT_FRAMES_IN_FLIGHT
+    int next_lane = 0, last_lane = 0;
+    int windows_alloc = 0;                 // slot windows the pyramid allocation holds
+    cudaEvent_t ev_user = nullptr;         // "everything the caller enqueued so far" on `stream`
     uint64_t launches = 0;
 };
 
@@ -115,23 +136,104 @@ struct DeviceGuard {
     }
 };
 
-int ensure_pyramid(rtce_ctx* c) {
-    const size_t need = c->slot_stride * (size_t)c->slots;
-    if (c->d_pyr && c->d_pyr_floats >= need && c->slots_alloc >= c->slots) return RTCE_OK;
+// Allocate what lane `l` needs (idempotent).
+int lane_init(rtce_ctx* c, int l) {
+    Lane& L = c->lanes[l];
+    if (L.ready) return RTCE_OK;
+    bool ok = cudaStreamCreateWithFlags(&L.st, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreateWithFlags(&L.ev_fork, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&L.ev_done, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&L.ev_free, cudaEventDisableTiming) == cudaSuccess;
+    for (int g = 0; ok && g < kMaxGroups; g++)
+        ok = cudaStreamCreateWithFlags(&L.grp_stream[g], cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&L.ev_join[g], cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < kCamRing; i++) ok = cudaEventCreateWithFlags(&L.ev_cam[i], cudaEventDisableTiming) == cudaSuccess;
+    ok = ok && cudaMalloc(&L.d_tickets, sizeof(int) * kMaxGroups * kMaxLevels * 4) == cudaSuccess &&
+         cudaMalloc(&L.d_cams, sizeof(Cam) * kMaxBatch) == cudaSuccess &&
+         cudaMallocHost(&L.h_cams, sizeof(Cam) * kMaxBatch * kCamRing) == cudaSuccess &&
+         cudaMalloc(&L.d_oq, sizeof(float) * kMaxGroups * (size_t)kOverflowCap * (10 + kSmallSceneMax)) == cudaSuccess;
+    if (!ok) {
+        cudaGetLastError();
+        return fail(c, RTCE_ERR_NOMEM, "lane resources");
+    }
+    L.ready = true;
+    return RTCE_OK;
+}
+
+void lane_free(Lane& L) {
+    if (L.st) cudaStreamSynchronize(L.st);
+    for (int g = 0; g < kMaxGroups; g++) {
+        if (L.grp_stream[g]) { cudaStreamSynchronize(L.grp_stream[g]); cudaStreamDestroy(L.grp_stream[g]); }
+        if (L.ev_join[g]) cudaEventDestroy(L.ev_join[g]);
+    }
+    for (auto& g : L.graphs) cudaGraphExecDestroy(g.exec);
+    L.graphs.clear();
+    for (int i = 0; i < kCamRing; i++)
+        if (L.ev_cam[i]) cudaEventDestroy(L.ev_cam[i]);
+    if (L.ev_fork) cudaEventDestroy(L.ev_fork);
+    if (L.ev_done) cudaEventDestroy(L.ev_done);
+    if (L.ev_free) cudaEventDestroy(L.ev_free);
+    if (L.d_cams) cudaFree(L.d_cams);
+    if (L.h_cams) cudaFreeHost(L.h_cams);
+    if (L.d_tickets) cudaFree(L.d_tickets);
+    if (L.d_oq) cudaFree(L.d_oq);
+    if (L.st) cudaStreamDestroy(L.st);
+    L = Lane();
+}
+
+// Make the context's stream wait for every lane that has traced since it last did (stream-level, the host
+// does not block): after this, work enqueued on the context's stream sees every image traced so far.
+int flush_lanes(rtce_ctx* c) {
+    for (int l = 0; l < kMaxLanes; l++) {
+        Lane& L = c->lanes[l];
+        if (L.ready && L.pending) {
+            RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, L.ev_done, 0));
+            L.pending = false;
+        }
+    }
+    return RTCE_OK;
+}
+
+// Everything issued so far has finished (host blocks).
+int quiesce(rtce_ctx* c) {
+    int r = flush_lanes(c);
+    if (r) return r;
+    RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RTCE_OK;
+}
+
+// The pyramid allocation holds `windows` windows of c->slots frame slots (window w belongs to lane w).
+int ensure_pyramid(rtce_ctx* c, int windows = 1) {
+    windows = std::max(windows, std::max(1, c->windows_alloc));   // never shrink: a lane's graphs point into its window
+    const size_t need = c->slot_stride * (size_t)c->slots * (size_t)windows;
+    if (c->d_pyr && c->d_pyr_floats >= need && c->slots_alloc == c->slots && c->windows_alloc >= windows) return RTCE_OK;
+    int r = quiesce(c);
+    if (r) return r;
     if (c->d_pyr) {
-        RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
         RTCE_CUDA(c, cudaFree(c->d_pyr));
         c->d_pyr = nullptr;
+        c->d_pyr_floats = 0;
     }
     cudaError_t e = cudaMalloc(&c->d_pyr, need * sizeof(float));
-    if (e != cudaSuccess) return fail(c, RTCE_ERR_NOMEM, "cudaMalloc(pyramid)", e);
+    if (e != cudaSuccess) {
+        c->windows_alloc = 0;
+        c->slots_alloc = 0;
+        return fail(c, RTCE_ERR_NOMEM, "cudaMalloc(pyramid)", e);
+    }
     c->plan_version++;
     c->d_pyr_floats = need;
     c->slots_alloc = c->slots;
+    c->windows_alloc = windows;
     // the reference clears every level image before its dispatch (main.rs:312); texels outside a
     // set rect are never written by the pass, so clear once here to give them the same value
     RTCE_CUDA(c, cudaMemsetAsync(c->d_pyr, 0, need * sizeof(float), c->stream));
+    RTCE_CUDA(c, cudaStreamSynchronize(c->stream));   // lanes on other streams start from the cleared allocation
     return RTCE_OK;
+}
+
+// First float of frame slot `slot` of window `w`.
+inline float* window_slot(const rtce_ctx* c, int w, int slot) {
+    return c->d_pyr + ((size_t)w * (size_t)c->slots + (size_t)slot) * c->slot_stride;
 }
 
 }  // namespace
@@ -166,19 +268,10 @@ int rtce_create(int device, float render_dist, rtce_ctx** out) {
     c->device = device;
     c->render_dist = render_dist;
     DeviceGuard g(device);
-    bool grp_ok = true;
-    for (int g = 0; g < kMaxGroups; g++) {
-        grp_ok = grp_ok && cudaStreamCreateWithFlags(&c->grp_stream[g], cudaStreamNonBlocking) == cudaSuccess &&
-                 cudaEventCreateWithFlags(&c->ev_join[g], cudaEventDisableTiming) == cudaSuccess;
-    }
-    if (!grp_ok || cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaMalloc(&c->d_counters, 4 * kMaxLevels * sizeof(unsigned long long)) != cudaSuccess ||
-        cudaMalloc(&c->d_tickets, sizeof(int) * kMaxGroups * kMaxLevels * 4) != cudaSuccess ||
-        cudaMalloc(&c->d_cams, sizeof(Cam) * kMaxBatch) != cudaSuccess ||
-        cudaMallocHost(&c->h_cams, sizeof(Cam) * kMaxBatch * rtce_ctx::kCamRing) != cudaSuccess ||
-        cudaMalloc(&c->d_oq, sizeof(float) * kMaxGroups * (size_t)kOverflowCap * (10 + kSmallSceneMax)) != cudaSuccess) {
+        cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming) != cudaSuccess ||
+        cudaMalloc(&c->d_counters, 4 * kMaxLevels * sizeof(unsigned long long)) != cudaSuccess || lane_init(c, 0) != RTCE_OK) {
         rtce_destroy(c);
         return RTCE_ERR_CUDA;
     }
@@ -186,7 +279,6 @@ int rtce_create(int device, float render_dist, rtce_ctx** out) {
         cudaEventCreateWithFlags(&c->ev_traced[i], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming);
     }
-    for (int i = 0; i < rtce_ctx::kCamRing; i++) cudaEventCreateWithFlags(&c->ev_cam[i], cudaEventDisableTiming);
     c->stream = c->own_stream;
     *out = c;
     return RTCE_OK;
@@ -197,17 +289,8 @@ void rtce_destroy(rtce_ctx* c) {
     DeviceGuard g(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
-    for (int g = 0; g < kMaxGroups; g++) {
-        if (c->grp_stream[g]) cudaStreamSynchronize(c->grp_stream[g]);
-        if (c->ev_join[g]) cudaEventDestroy(c->ev_join[g]);
-    }
-    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
-    for (auto& g : c->graphs) cudaGraphExecDestroy(g.exec);
-    c->graphs.clear();
-    for (int i = 0; i < rtce_ctx::kCamRing; i++)
-        if (c->ev_cam[i]) cudaEventDestroy(c->ev_cam[i]);
-    if (c->d_cams) cudaFree(c->d_cams);
-    if (c->h_cams) cudaFreeHost(c->h_cams);
+    for (int l = 0; l < kMaxLanes; l++) lane_free(c->lanes[l]);
+    if (c->ev_user) cudaEventDestroy(c->ev_user);
     for (int i = 0; i < 2; i++) {
         if (c->ev_traced[i]) cudaEventDestroy(c->ev_traced[i]);
         if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
@@ -216,20 +299,26 @@ void rtce_destroy(rtce_ctx* c) {
     if (c->d_accum) cudaFree(c->d_accum);
     if (c->d_spheres) cudaFree(c->d_spheres);
     if (c->d_counters) cudaFree(c->d_counters);
-    if (c->d_tickets) cudaFree(c->d_tickets);
-    if (c->d_oq) cudaFree(c->d_oq);
     if (c->d_dbg) cudaFree(c->d_dbg);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
-    for (int g = 0; g < kMaxGroups; g++)
-        if (c->grp_stream[g]) cudaStreamDestroy(c->grp_stream[g]);
     delete c;
 }
 
 int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
     if (!c) return RTCE_ERR_INVALID;
+    {
+        DeviceGuard g(c->device);
+        int r = flush_lanes(c);   // batches in flight were issued under the old options; order them before what follows
+        if (r) return r;
+    }
     c->plan_version++;
     switch (option) {
+        case RTCE_OPT_FRAMES_IN_FLIGHT:
+            if (value < 1 || value > kMaxLanes) return fail(c, RTCE_ERR_INVALID, "frames in flight out of range");
+            c->in_flight = (int)value;
+            c->next_lane = 0;
+            return RTCE_OK;
         case RTCE_OPT_GRAPH: c->use_graph = value != 0; return RTCE_OK;
         case RTCE_OPT_COUNTERS: c->count = value != 0; return RTCE_OK;
         case RTCE_OPT_FRAME_SLOTS:
@@ -253,7 +342,7 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             c->coarse_mode = (int)value;
             return RTCE_OK;
         case RTCE_OPT_GROUPS:
-            if (value < 1 || value > kMaxGroups) return fail(c, RTCE_ERR_INVALID, "groups out of range");
+            if (value < 0 || value > kMaxGroups) return fail(c, RTCE_ERR_INVALID, "groups out of range");
             c->groups = (int)value;
             return RTCE_OK;
         case RTCE_OPT_STRIP_MIN_RAYS:
@@ -267,7 +356,8 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
 int rtce_set_stream(rtce_ctx* c, void* cuda_stream) {
     if (!c) return RTCE_ERR_INVALID;
     DeviceGuard g(c->device);
-    RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+    int r = quiesce(c);
+    if (r) return r;
     c->plan_version++;
     c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
     return RTCE_OK;
@@ -277,6 +367,9 @@ int rtce_set_spheres(rtce_ctx* c, const rtce_sphere* spheres, uint32_t n) {
     if (!c || (n && !spheres)) return fail(c, RTCE_ERR_INVALID, "rtce_set_spheres: null");
     if (n > RTCE_MAX_SPHERES) return fail(c, RTCE_ERR_LIMIT, "rtce_set_spheres: n > RTCE_MAX_SPHERES");
     DeviceGuard g(c->device);
+    int r = flush_lanes(c);
+    if (r) return r;
+    if (n > (uint32_t)kSmallSceneMax && (r = quiesce(c))) return r;   // the sphere buffer is about to be rewritten
     c->plan_version++;
     c->n_spheres = (int)n;
     memset(c->small, 0, sizeof(c->small));
@@ -353,13 +446,14 @@ int rtce_set_view(rtce_ctx* c, const rtce_constant_buffer* cb, int levels) {
     memcpy(c->lh, lh, sizeof(lh));
     memcpy(c->loff, loff, sizeof(loff));
     const bool same = c->have_view && c->slot_stride == off;
+    int r = quiesce(c);   // nothing in flight reads the old geometry past this point
+    if (r) return r;
     c->slot_stride = off;
     c->rect[0] = c->rect[1] = c->rect[2] = c->rect[3] = 0;
     c->have_view = true;
     if (!same) {
         c->d_pyr_floats = 0;   // force re-allocation (and the clear)
         if (c->d_pyr) {
-            RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
             RTCE_CUDA(c, cudaFree(c->d_pyr));
             c->d_pyr = nullptr;
         }
@@ -371,6 +465,11 @@ int rtce_set_rect(rtce_ctx* c, int x0, int y0, int x1, int y1) {
     if (!c) return RTCE_ERR_INVALID;
     if (!c->have_view) return fail(c, RTCE_ERR_STATE, "rtce_set_rect: view not set");
     const int W = c->lw[c->levels - 1], H = c->lh[c->levels - 1];
+    {
+        DeviceGuard g(c->device);
+        int r = flush_lanes(c);
+        if (r) return r;
+    }
     c->plan_version++;
     if (x0 == 0 && y0 == 0 && x1 == 0 && y1 == 0) {
         c->rect[0] = c->rect[1] = c->rect[2] = c->rect[3] = 0;
@@ -390,7 +489,7 @@ int rtce_level_info(const rtce_ctx* c, int level, int slot, int* w, int* h, floa
     if (level < 0 || level >= c->levels || slot < 0 || slot >= c->slots) return RTCE_ERR_INVALID;
     if (w) *w = c->lw[level];
     if (h) *h = c->lh[level];
-    if (dptr) *dptr = c->d_pyr + (size_t)slot * c->slot_stride + c->loff[level];
+    if (dptr) *dptr = window_slot(c, c->last_lane, slot) + c->loff[level];   // the window of the latest batch
     return RTCE_OK;
 }
 

@@ -18,6 +18,7 @@ LIB_PATH = os.path.join(_HERE, "librtce.so")
 RTCE_OK = 0
 OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS, OPT_COARSE_FUSED, OPT_STRIP_ROWS = 1, 2, 3, 4, 5, 6, 7
 OPT_GRAPH = 8
+OPT_FRAMES_IN_FLIGHT = 9
 KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED, KERNEL_STRIP = 0, 1, 2, 3
 
 # compute.glsl:7-12 PushConstantData, 40 bytes
@@ -32,7 +33,7 @@ EXPORTS = [
     "rtce_set_rect", "rtce_level_count", "rtce_level_info", "rtce_host_level_count",
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
     "rtce_trace_accumulate", "rtce_accum_info", "rtce_readback", "rtce_readback_accum",
-    "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_get_counters",
+    "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_flush", "rtce_get_counters",
     "rtce_get_level_counters",
     "rtce_measure_fp32_issue", "rtce_selftest_math", "rtce_debug_strip_timeline",
     "rtce_debug_launch_timeline",
@@ -88,6 +89,7 @@ def load_library() -> C.CDLL:
         "rtce_host_alloc": (i32, [C.POINTER(vp), sz]),
         "rtce_host_free": (i32, [vp]),
         "rtce_sync": (i32, [vp]),
+        "rtce_flush": (i32, [vp]),
         "rtce_get_counters": (i32, [vp, C.POINTER(_Counters)]),
         "rtce_get_level_counters": (i32, [vp, i32, C.POINTER(_Counters)]),
         "rtce_measure_fp32_issue": (i32, [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
@@ -271,6 +273,10 @@ class Engine:
 
     def sync(self):
         self._check(self.lib.rtce_sync(self._ctx), "rtce_sync")
+
+    def flush(self):
+        """Frames in flight: order the context's stream after every batch traced so far (no host wait)."""
+        self._check(self.lib.rtce_flush(self._ctx), "rtce_flush")
 
     def readback(self, level: int = -1, slot: int = 0) -> np.ndarray:
         w, h, _ = self.level_info(level, slot)

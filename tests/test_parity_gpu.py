@@ -230,6 +230,62 @@ def test_graph_replay_equals_issued_launches(groups, case_table):
     assert np.array_equal(_bits(gc[1]), _bits(ref[-1]))
 
 
+@pytest.mark.parametrize("in_flight", [2, 3, 4])
+def test_frames_in_flight_equal_strict_order(in_flight, case_table):
+    """RTCE_OPT_FRAMES_IN_FLIGHT: batches rotating over windows of slots on their own streams give the bits of
+    strict stream order, every window keeps its batch until it is reused, and a scene change in between lands
+    between the right batches."""
+    case = case_table["default_800x600"]
+    rots, poss = camera.bench_camera_path(40)
+    pcs = rt.make_push_constants(rots, poss)
+    moved = np.array(case[2], np.float32).copy()
+    moved[:, 1] -= 0.5
+    with _engine(case, slots=4) as e:                   # strict order: the expected images
+        want = []
+        for k in range(10):
+            if k == 6:
+                e.set_spheres(moved)
+            e.trace(pcs[4 * k:4 * k + 4])
+            want.append([e.readback(-1, j) for j in range(4)])
+    with _engine(case, slots=4) as e:
+        e.set_option(rt.OPT_FRAMES_IN_FLIGHT, in_flight)
+        for k in range(10):
+            if k == 6:
+                e.set_spheres(moved)
+            e.trace(pcs[4 * k:4 * k + 4])
+            if k in (0, 3, 5, 6, 9):                    # reads in between (flush) and calls issued back to back
+                for j in range(4):
+                    assert np.array_equal(_bits(e.readback(-1, j)), _bits(want[k][j])), (k, j)
+        e.flush()
+        e.sync()
+        lv = [e.readback(i, 2) for i in range(e.levels)]
+        assert np.array_equal(_bits(lv[-1]), _bits(want[9][2]))
+        # back to one frame in flight: strict order again, window 0
+        e.set_option(rt.OPT_FRAMES_IN_FLIGHT, 1)
+        e.trace(pcs[0:4])
+        e.set_spheres(case[2])
+        e.trace(pcs[4:8])
+        assert np.array_equal(_bits(e.readback(-1, 1)), _bits(want[1][1]))
+
+
+def test_accumulate_lanes_equal_single_lane(case_table):
+    """rtce_trace_accumulate: chunks rotating over three lanes == one chunk at a time (counters on: one lane)."""
+    case = case_table["default_800x600"]
+    rots, poss = camera.bench_camera_path(23)
+    pcs = rt.make_push_constants(rots, poss)
+    with _engine(case, slots=4) as e:
+        e.trace_accumulate(pcs)                         # 6 chunks over 3 lanes
+        a = e.readback_accum()
+        e.trace_accumulate(pcs[:9])                     # again, lanes warm, ragged end
+        a9 = e.readback_accum()
+    with _engine(case, slots=4, count=True) as e:
+        e.trace_accumulate(pcs)
+        b = e.readback_accum()
+        e.trace_accumulate(pcs[:9])
+        b9 = e.readback_accum()
+    assert np.array_equal(_bits(a), _bits(b)) and np.array_equal(_bits(a9), _bits(b9))
+
+
 def test_large_scene_kernel_matches_checker():
     """objCount > 8 (CTA-per-ray kernel) on a bigger synthetic scene than the golden cases."""
     o = oracle.best()
