@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--in-flight", type=int, default=None,
                     help="RTCE_OPT_FRAMES_IN_FLIGHT for frame-by-frame workloads (default 4): batches of consecutive steps "
                          "rotate over this many windows of frame slots and overlap on the device; 1 = strict stream order")
+    ap.add_argument("--strip-ctas", type=int, default=None, help="RTCE_OPT_STRIP_CTAS_PER_SM")
     ap.add_argument("--graph", type=int, default=None, help="RTCE_OPT_GRAPH: 1 = replay the launch chain from a CUDA graph (default), 0 = issue every launch")
     ap.add_argument("--frames", type=int, default=None, help="override frames per step (labelled in config)")
     ap.add_argument("--levels", type=int, default=None, help="override pyramid levels (configs[3] sweep)")
@@ -259,6 +260,8 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_STRIP_ROWS, args.strip_rows)
     if args.graph is not None:
         eng.set_option(rt.OPT_GRAPH, args.graph)
+    if args.strip_ctas is not None:
+        eng.set_option(rt.OPT_STRIP_CTAS_PER_SM, args.strip_ctas)
     in_flight = 1 if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 4)
     eng.set_option(rt.OPT_FRAMES_IN_FLIGHT, in_flight)
     slots = min(frames_rank, 16)
@@ -414,7 +417,7 @@ def run_ours(args, wl):
             d2h = int(tb.item())
         e2e = {"value": units_per_step / dt / 1e6, "unit": "Mrays/s", "ms_per_step": dt * 1e3,
                "h2d_bytes_per_step": int(pcs.nbytes) * world, "d2h_bytes_per_step": int(d2h), "steps": k_e2e,
-               "note": "host PushConstantData in (passed by value into kernel parameters), every frame's final level "
+               "note": "host PushConstantData in (staged through a pinned ring into the device camera buffer), every frame's final level "
                        "copied to pinned host memory (accumulate workloads: the one accumulated image); N>1: each rank "
                        "returns its own frames (accumulate workloads: its row band) to its host buffer"}
 
@@ -492,7 +495,7 @@ def run_ours(args, wl):
                                    f"{n_gpus} row bands of the final level + one NCCL gather of the accumulated image to rank 0 per step"),
                    "frames_in_flight": in_flight if not wl["accumulate"] else "3 chunks (internal to rtce_trace_accumulate)",
                    "l2": f"no flush: each step rewrites {bytes_step / 1e6:.0f} MB of pyramid (> 126 MB L2 when frames >= 12 at 1080p); parents are meant to be L2 hits",
-                   "kernel": {0: "auto (strip + fused coarse levels)", 1: "per-level", 2: "fused", 3: "strip + fused coarse levels"}[args.kernel]},
+                   "kernel": {0: "auto (strip kernel + overflow launch per fine level, one per-pixel launch per coarse level)", 1: "per-level", 2: "fused", 3: "strip kernel + overflow launch per fine level, one per-pixel launch per coarse level"}[args.kernel]},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps) * n_gpus,
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "mprimary_per_s": Wf * Hf * frames / (ms_step * 1e-3) / 1e6,

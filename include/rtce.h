@@ -99,7 +99,7 @@ typedef enum rtce_option {
                                    thread-block cluster per frame walks the levels with a cluster barrier in between
                                    (fewest launches; measured slower on B200 at 1080p: a frame is confined to 8 SMs) */
     RTCE_OPT_STRIP_ROWS = 7,    /* kernel plan 3: rows of a strip-kernel task (a task is 32 columns x this many rows), 1..32 */
-    RTCE_OPT_FRAMES_IN_FLIGHT = 9, /* 1..4, default 1.  The reference keeps frames in flight behind its swapchain
+    RTCE_OPT_FRAMES_IN_FLIGHT = 9, /* 1..8, default 1.  The reference keeps frames in flight behind its swapchain
                                    (main.rs:859-884: acquire, submit, fence of the PREVIOUS frame).  With W > 1 successive
                                    rtce_trace_batch calls rotate over W windows of frame slots, each with its own streams:
                                    a call starts after everything enqueued on the context's stream so far, but NOT after
@@ -108,6 +108,8 @@ typedef enum rtce_option {
                                    batch whose window the next call reuses; rtce_flush (stream-level) or rtce_sync /
                                    rtce_readback* (host-level) order it after everything.  rtce_level_info and
                                    rtce_readback address the window of the latest call.  W = 1 is strict stream order. */
+    RTCE_OPT_STRIP_CTAS_PER_SM = 10, /* kernel plan 3: persistent CTAs per SM of a strip launch; 0 (default) = every resident
+                                   slot (3 on B200).  Fewer leave room for the launches of other lanes in flight. */
     RTCE_OPT_GRAPH = 8,         /* kernel plan 3: 1 (default) = the launch chain of a frame batch (every level of every group,
                                    forks and joins included) is captured once into a CUDA graph and replayed by later
                                    calls with the same batch shape; the per-call cameras travel through device memory.

@@ -25,7 +25,7 @@ static constexpr unsigned kOverflowCap = 1u << 19;   // rays per frame group (38
 // successive rtce_trace_batch calls rotate over the lanes and overlap on the device — the
 // latency-bound coarse levels and long-ray launches of one batch run under the issue-bound final
 // level of another — and rtce_trace_accumulate rotates its chunks the same way.
-static constexpr int kMaxLanes = 4;
+static constexpr int kMaxLanes = 8;
 static constexpr int kCamRing = 8;
 struct ChunkGraph { int frames, slot0; bool own_stream; uint64_t version; cudaGraphExec_t exec; uint64_t launches; };
 struct Lane {
@@ -56,6 +56,7 @@ struct rtce_ctx {
     int groups = 0;                      // RTCE_OPT_GROUPS (0 = auto)
     int coarse_mode = 0;                 // RTCE_OPT_COARSE_FUSED: 0 one launch per level, 1 fused-pyramid kernel, 2 cluster kernel
     int strip_rows = 16;                 // RTCE_OPT_STRIP_ROWS
+    int strip_ctas_per_sm = 0;           // RTCE_OPT_STRIP_CTAS_PER_SM (0 = every resident slot)
     // diagnostics (rtce_debug_launch_timeline): an event pair around every kernel launch
     struct LaunchMark { cudaEvent_t e0, e1; int kind, level, group; };
     bool mark_launches = false;
@@ -336,6 +337,10 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
         case RTCE_OPT_STRIP_ROWS:
             if (value < 1 || value > kStripMaxRows) return fail(c, RTCE_ERR_INVALID, "strip rows out of range");
             c->strip_rows = (int)value;
+            return RTCE_OK;
+        case RTCE_OPT_STRIP_CTAS_PER_SM:
+            if (value < 0 || value > 8) return fail(c, RTCE_ERR_INVALID, "strip CTAs per SM out of range");
+            c->strip_ctas_per_sm = (int)value;
             return RTCE_OK;
         case RTCE_OPT_COARSE_FUSED:
             if (value < 0 || value > 2) return fail(c, RTCE_ERR_INVALID, "coarse plan out of range");

@@ -129,6 +129,7 @@ struct StripParams {
     int ntx, nty;             // tasks per frame: 32-wide columns x `rows`-high rows covering the ROI
     int rows;                 // rows per task, 1..kStripMaxRows
     int cta_share;            // launch 1/cta_share of the resident CTA slots (>= 1)
+    int ctas_per_sm;          // > 0: launch at most this many CTAs per SM (leaves room for other lanes' launches)
     int frames;
     int n_spheres;
     float isx, isy, ratx, raty, threshold, render_dist;

@@ -429,6 +429,7 @@ static cudaError_t launch_strip_ncp(const StripParams& p, cudaStream_t st) {
     const int smem = (kStripThreads / 32) * (RTCE_SQ_WORDS(N) * kQCap + 4 * kStripMaxRows + kPinWords) * (int)sizeof(float);
     static bool configured = false;   // per instantiation
     static int resident = 148 * 3;    // CTAs the device holds at once
+    static int n_sms = 148;
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(k_trace_strip<N, COUNT, HAS_PARENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
@@ -440,11 +441,13 @@ static cudaError_t launch_strip_ncp(const StripParams& p, cudaStream_t st) {
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_strip<N, COUNT, HAS_PARENT>, kStripThreads, smem);
         if (e != cudaSuccess) return e;
         resident = sms * (per_sm > 0 ? per_sm : 1);
+        n_sms = sms;
         configured = true;
     }
     // persistent CTAs: one resident wave for the whole batch
     const long long tasks = (long long)p.ntx * p.nty * p.frames;
     long long ctas = resident / (p.cta_share > 1 ? p.cta_share : 1);
+    if (p.ctas_per_sm > 0 && ctas > (long long)n_sms * p.ctas_per_sm) ctas = (long long)n_sms * p.ctas_per_sm;
     if (ctas < 1) ctas = 1;
     const long long need = (tasks + kStripThreads / 32 - 1) / (kStripThreads / 32);
     if (ctas > need) ctas = need;

@@ -73,6 +73,7 @@ extern "C" {
     fn rtce_readback(ctx: *mut rtce_ctx, level: c_int, slot: c_int, host: *mut f32, pitch_bytes: usize) -> c_int;
     fn rtce_render_to_host(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int, host_out: *mut f32) -> c_int;
     fn rtce_sync(ctx: *mut rtce_ctx) -> c_int;
+    fn rtce_flush(ctx: *mut rtce_ctx) -> c_int;
     fn rtce_get_counters(ctx: *mut rtce_ctx, out: *mut Counters) -> c_int;
 }
 
@@ -149,6 +150,19 @@ impl ConeMarcher {
     /// Fence wait (src/main.rs:882-884).
     pub fn sync(&mut self) -> Result<(), Error> {
         let st = unsafe { rtce_sync(self.ctx) };
+        self.check(st)
+    }
+
+    /// Frames in flight (src/main.rs:859-884): `w` batches rotate over `w` windows of frame slots
+    /// (RTCE_OPT_FRAMES_IN_FLIGHT = 9); 1 = strict stream order.
+    pub fn set_frames_in_flight(&mut self, w: u32) -> Result<(), Error> {
+        let st = unsafe { rtce_set_option(self.ctx, 9, w as i64) };
+        self.check(st)
+    }
+
+    /// Order the context's stream after every batch traced so far (no host wait).
+    pub fn flush(&mut self) -> Result<(), Error> {
+        let st = unsafe { rtce_flush(self.ctx) };
         self.check(st)
     }
 }
