@@ -172,6 +172,21 @@ int rtce_accum_info(const rtce_ctx* ctx, int* w, int* h, float** device_ptr);
  * Headless readback; both synchronise.  pitch_bytes = 0 -> tightly packed rows. */
 int rtce_readback(rtce_ctx* ctx, int level, int slot, float* host, size_t pitch_bytes);
 int rtce_readback_accum(rtce_ctx* ctx, float* host, size_t pitch_bytes);
+/* -- the presentation shading pass ---------------------------------------------
+ * Replaces the draw of get_command_buffer's render-pass half (main.rs:318-338: fullscreen triangle of
+ * vertex.glsl:3-10, one fragment per window pixel running fragment.glsl:123-187): shades the final pyramid
+ * level of frame slots 0 .. frames-1 of the latest batch with the SAME push constants the batch was traced
+ * with (the reference pushes one PushConstantData to both pipelines, main.rs:296-299, 327-331) into RGBA32F
+ * colour slots owned by the context — the headless stand-in for the swapchain image.  Needs the materials and
+ * lights of rtce_set_scene.  pow() is pinned (csrc/rtce_shade_math.cuh); fragColor.a, which the shader never
+ * writes, is 1.  rtce_readback_color_rgba8 converts like a UNORM attachment (clamp, x255, round to nearest even).
+ * Counters (RTCE_OPT_COUNTERS): {pixels, hit pixels, distance() calls, light evaluations}. */
+int rtce_shade_batch(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
+int rtce_color_info(const rtce_ctx* ctx, int slot, int* w, int* h, float** device_rgba32f);
+int rtce_readback_color(rtce_ctx* ctx, int slot, float* host_rgba32f);
+int rtce_readback_color_rgba8(rtce_ctx* ctx, int slot, unsigned char* host_rgba8);
+int rtce_get_shade_counters(rtce_ctx* ctx, uint64_t out[4]);
+
 /* End-to-end convenience used by headless callers: trace `frames` frames from HOST push constants
  * and copy every frame's final level to `host_out` (frames * w * h floats), copies overlapped
  * with the tracing of later frames.  Synchronises before returning. */

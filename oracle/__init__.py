@@ -10,6 +10,10 @@ Three checkers share one calling convention (see ``oracle/ref_driver.cpp``):
             utilities.glsl compiled as C++ (<= 8 spheres, <= 9 levels, RENDER_DIST 1000)
 * ``refx``  oracle/_ref/librtce_ref_ext.so  same text, MAX_OBJECTS / imgs[] raised
 * ``port``  oracle/librtce_oracle.so        plain-C restatement (any size)
+
+The presentation shading pass (fragment.glsl) has the same pair: ``Oracle.shade`` of
+``ref`` / ``refx`` runs oracle/_ref/librtce_ref_frag.so (the reference's fragment.glsl compiled as C++),
+of ``port`` the C restatement in rtce_oracle_shade.c.
 """
 from __future__ import annotations
 
@@ -25,6 +29,7 @@ _LIBS = {
     "refx": (os.path.join(_HERE, "_ref", "librtce_ref_ext.so"), "rtce_refx"),
     "port": (os.path.join(_HERE, "librtce_oracle.so"), "rtce_oracle"),
 }
+_FRAG_LIB = os.path.join(_HERE, "_ref", "librtce_ref_frag.so")
 _loaded: dict = {}
 
 
@@ -66,6 +71,41 @@ class Oracle:
         self.max_levels = g("max_levels")()
         self.fixed_render_dist = g("render_dist")()
 
+    def _shade_fn(self):
+        if getattr(self, "_shade", None) is None:
+            if self.kind == "port":
+                fn = self.lib.rtce_oracle_shade
+            else:
+                if not os.path.exists(_FRAG_LIB):
+                    raise FileNotFoundError(f"{_FRAG_LIB} not built (run `make -C oracle`)")
+                self._frag = C.CDLL(_FRAG_LIB)
+                fn = self._frag.rtce_ref_shade
+            fn.restype = C.c_int
+            fn.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_int,
+                           C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+            self._shade = fn
+        return self._shade
+
+    def shade(self, mutable_data: bytes, view, ratio, rot, pos, depth, render_dist=1000.0, threads=0):
+        """Presentation shading pass of one frame: depth [h, w] float32 (the final pyramid level, at least the
+        window's size) -> (rgba float32 [view_h, view_w, 4], counters {P pixels, H hit pixels, D distance() calls, L light evaluations})."""
+        depth = np.ascontiguousarray(depth, dtype=np.float32)
+        h, w = depth.shape
+        md = np.frombuffer(bytes(mutable_data), dtype=np.uint8).copy()
+        if md.size != 656:
+            raise ValueError("MutableData is 656 bytes (std140)")
+        view = np.ascontiguousarray(view, dtype=np.float32)
+        ratio = np.ascontiguousarray(ratio, dtype=np.float32)
+        rot = np.ascontiguousarray(rot, dtype=np.float32)
+        pos = np.ascontiguousarray(pos, dtype=np.float32)
+        out = np.zeros((int(view[1]), int(view[0]), 4), dtype=np.float32)
+        cnt = (C.c_ulonglong * 4)()
+        err = self._shade_fn()(md.ctypes.data, view.ctypes.data, ratio.ctypes.data, rot.ctypes.data, pos.ctypes.data,
+                               float(render_dist), depth.ctypes.data, w, h, int(threads), out.ctypes.data, cnt)
+        if err != 0:
+            raise RuntimeError(f"oracle[{self.kind}] shade failed: {err}")
+        return out, {"P": int(cnt[0]), "H": int(cnt[1]), "D": int(cnt[2]), "L": int(cnt[3])}
+
     def level_count(self, view_w: float, resize_rule: bool = False) -> int:
         return int(self._level_count(view_w, int(resize_rule)))
 
@@ -104,6 +144,24 @@ class Oracle:
         if err != 0:
             raise RuntimeError(f"oracle[{self.kind}] trace failed: {err}")
         return imgs, {"R": int(cnt[0]), "E": int(cnt[1]), "S": int(cnt[2])}
+
+
+def rgba8(rgba: np.ndarray) -> np.ndarray:
+    """RGBA32F -> RGBA8 UNORM with the pinned conversion (rtce_pinned_math.h), via the C port."""
+    lib = load("port").lib
+    lib.rtce_oracle_rgba8.restype = None
+    lib.rtce_oracle_rgba8.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+    a = np.ascontiguousarray(rgba, dtype=np.float32)
+    out = np.zeros(a.shape, dtype=np.uint8)
+    lib.rtce_oracle_rgba8(a.ctypes.data, a.size // 4, out.ctypes.data)
+    return out
+
+
+def pinned_pow(x: float, y: float) -> float:
+    lib = load("port").lib
+    lib.rtce_oracle_pinned_pow.restype = C.c_float
+    lib.rtce_oracle_pinned_pow.argtypes = [C.c_float, C.c_float]
+    return float(lib.rtce_oracle_pinned_pow(x, y))
 
 
 def load(kind: str) -> Oracle:

@@ -76,12 +76,20 @@ struct vec3 {
     vec3(float a, float b, float c) : x(a), y(b), z(c) {}
     explicit vec3(float a) : x(a), y(a), z(a) {}
 };
-struct vec3_view { float x, y, z; operator vec3() const { return vec3(x, y, z); } };
+struct vec3_view {
+    float x, y, z;
+    operator vec3() const { return vec3(x, y, z); }
+    vec3_view& operator=(const vec3& v) { x = v.x; y = v.y; z = v.z; return *this; }           // fragColor.rgb = ...
+    vec3_view& operator+=(const vec3& v) { x = x + v.x; y = y + v.y; z = z + v.z; return *this; }   // fragColor.rgb += ...
+};
+struct vec2_view { float x, y; operator vec2() const { return vec2(x, y); } };
 struct vec4 {
     union {
         struct { float x, y, z, w; };
         struct { float r, g, b, a; };
         struct { vec3_view xyz; float w_; };
+        struct { vec3_view rgb; float a_; };
+        struct { vec2_view xy; float z_, w2_; };
     };
     vec4() = default;
     vec4(float a, float b, float c, float d) : x(a), y(b), z(c), w(d) {}
@@ -95,6 +103,8 @@ inline vec2 operator*(const uvec2& a, const vec2& b) { return vec2((float)a.x * 
 inline vec2 operator*(const uvec2& a, float s) { return vec2((float)a.x * s, (float)a.y * s); }
 inline vec2 operator-(const vec2& a, float s) { return vec2(a.x - s, a.y - s); }
 inline vec2 operator*(const vec2& a, const vec2& b) { return vec2(a.x * b.x, a.y * b.y); }
+inline vec2 operator*(const vec2& a, int s) { return vec2(a.x * (float)s, a.y * (float)s); }   // fragment.glsl:126
+inline vec2 operator/(const vec2& a, const vec2& b) { return vec2(a.x / b.x, a.y / b.y); }
 
 inline vec3 operator+(const vec3& a, const vec3& b) { return vec3(a.x + b.x, a.y + b.y, a.z + b.z); }
 inline vec3 operator-(const vec3& a, const vec3& b) { return vec3(a.x - b.x, a.y - b.y, a.z - b.z); }
@@ -104,6 +114,7 @@ inline vec3 operator*(const vec3& a, float s) { return vec3(a.x * s, a.y * s, a.
 inline vec3 operator*(float s, const vec3& a) { return vec3(s * a.x, s * a.y, s * a.z); }
 inline vec3 operator/(const vec3& a, float s) { return vec3(a.x / s, a.y / s, a.z / s); }
 inline vec3 operator+(const vec3& a, float s) { return vec3(a.x + s, a.y + s, a.z + s); }
+inline vec3 operator+(float s, const vec3& a) { return vec3(s + a.x, s + a.y, s + a.z); }   // fragment.glsl:185
 inline vec3 operator-(const vec3& a, float s) { return vec3(a.x - s, a.y - s, a.z - s); }
 
 // ---- built-ins (canonical definitions, see header comment) ------------------
@@ -148,4 +159,7 @@ static const uvec3 gl_WorkGroupSize(8u, 8u, 1u);   // compute.glsl:5
 #define uniform struct
 #define readonly
 #define in
-#define main rtce_ref_shader_main
+#ifndef RTCE_SHADER_MAIN
+#define RTCE_SHADER_MAIN rtce_ref_shader_main
+#endif
+#define main RTCE_SHADER_MAIN

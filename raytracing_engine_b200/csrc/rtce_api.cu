@@ -87,6 +87,18 @@ struct rtce_ctx {
     float* d_accum = nullptr;
     size_t d_accum_floats = 0;
 
+    // presentation shading pass (fragment.glsl): the whole MutableData image, colour slots, staging
+    bool have_materials = false;             // rtce_set_scene was given the 656-byte image (rtce_set_spheres carries no materials / lights)
+    unsigned char md[RTCE_MUTABLE_DATA_SIZE] = {};
+    float4* d_color = nullptr;               // [slots][h][w] RGBA32F
+    size_t d_color_px = 0;                   // pixels per colour slot
+    int color_slots = 0;
+    uchar4* d_rgba8 = nullptr;               // one slot, for rtce_readback_color_rgba8
+    Cam* d_shade_cams = nullptr;             // [kMaxBatch]
+    Cam* h_shade_cams = nullptr;             // pinned
+    cudaEvent_t ev_shade_cams = nullptr;
+    unsigned long long* d_shade_counters = nullptr;   // {pixels, hit pixels, distance() calls, light evaluations}
+
     // options / counters
     bool count = false;
     int kernel_mode = 0;
@@ -301,6 +313,12 @@ void rtce_destroy(rtce_ctx* c) {
     if (c->d_spheres) cudaFree(c->d_spheres);
     if (c->d_counters) cudaFree(c->d_counters);
     if (c->d_dbg) cudaFree(c->d_dbg);
+    if (c->d_color) cudaFree(c->d_color);
+    if (c->d_rgba8) cudaFree(c->d_rgba8);
+    if (c->d_shade_cams) cudaFree(c->d_shade_cams);
+    if (c->h_shade_cams) cudaFreeHost(c->h_shade_cams);
+    if (c->ev_shade_cams) cudaEventDestroy(c->ev_shade_cams);
+    if (c->d_shade_counters) cudaFree(c->d_shade_counters);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     delete c;
@@ -376,6 +394,7 @@ int rtce_set_spheres(rtce_ctx* c, const rtce_sphere* spheres, uint32_t n) {
     if (r) return r;
     if (n > (uint32_t)kSmallSceneMax && (r = quiesce(c))) return r;   // the sphere buffer is about to be rewritten
     c->plan_version++;
+    c->have_materials = false;
     c->n_spheres = (int)n;
     memset(c->small, 0, sizeof(c->small));
     if (n <= (uint32_t)kSmallSceneMax) {
@@ -408,9 +427,16 @@ int rtce_set_scene(rtce_ctx* c, const void* md, size_t nbytes) {
     memcpy(&n, b + RTCE_MUTABLE_DATA_OBJCOUNT_OFFSET, 4);
     // the shader indexes objs[i] for i < objCount with objs[MAX_OBJECTS]; more than 8 is out of bounds there
     if (n > RTCE_REF_MAX_OBJECTS) return fail(c, RTCE_ERR_LIMIT, "rtce_set_scene: objCount > MAX_OBJECTS (8)");
+    uint32_t nl = 0;
+    memcpy(&nl, b + 8, 4);
+    if (nl > RTCE_REF_MAX_OBJECTS) return fail(c, RTCE_ERR_LIMIT, "rtce_set_scene: lightCount > MAX_LIGHTS (8)");
     rtce_sphere s[RTCE_REF_MAX_OBJECTS];
     memcpy(s, b + RTCE_MUTABLE_DATA_OBJS_OFFSET, sizeof(s));
-    return rtce_set_spheres(c, s, n);
+    int r = rtce_set_spheres(c, s, n);
+    if (r) return r;
+    memcpy(c->md, b, RTCE_MUTABLE_DATA_SIZE);   // materials and lights: the shading pass reads them (fragment.glsl:18-25)
+    c->have_materials = true;
+    return RTCE_OK;
 }
 
 int rtce_host_level_count(float view_w, int resize_rule) { return host_level_count(view_w, resize_rule != 0); }

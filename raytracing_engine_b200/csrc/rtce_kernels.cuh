@@ -155,6 +155,29 @@ struct OverflowParams {
 };
 cudaError_t launch_march_overflow(const OverflowParams& p, bool count, cudaStream_t st);
 
+// ---- presentation shading pass (fragment.glsl:123-187; objCount, lightCount <= 8) -----------------
+struct ShadeParams {
+    const float* depth;       // final pyramid level of frame slot 0 (binding 0)
+    float4* out;              // RGBA32F colour image of colour slot 0
+    size_t depth_stride;      // floats between frame slots
+    size_t out_stride;        // float4 between colour slots
+    unsigned long long* counters;   // {pixels, hit pixels, distance() calls, light evaluations} or nullptr
+    const Cam* cams;          // push constants rot / pos of every frame, device memory
+    int w, h;                 // final level image (pitch = w)
+    int out_w;                // pitch of the colour image = window width (cs.view.x <= w)
+    int x0, y0, x1, y1;       // rectangle of window pixels to shade
+    int n_obj, n_light;
+    float vw, vh, ratx, raty, render_dist;   // cs.view, cs.ratio, RENDER_DIST
+    float4 obj[kSmallSceneMax];    // objs[i] = {pos.xyz, size}
+    float4 matc[kSmallSceneMax];   // mats[i] = {color.rgb, shine}
+    float amb[kSmallSceneMax];     // mats[i].ambient
+    float4 lpos[kSmallSceneMax];   // lights[i].pos
+    float4 lcol[kSmallSceneMax];   // lights[i].color
+};
+cudaError_t launch_shade(const ShadeParams& p, int frames, bool count, cudaStream_t st);
+// RGBA32F -> RGBA8 UNORM (clamp, x255, round to nearest even)
+cudaError_t launch_rgba8(const float4* in, uchar4* out, size_t n, cudaStream_t st);
+
 // Accumulation extension: acc = (...((first ? 0 : acc) + img[0]) + img[1]) ... + img[frames-1], the images
 // `slot_stride` floats apart, added in frame order in one pass; and the final scale by 1/frames.
 cudaError_t launch_accumulate(float* acc, const float* img, size_t slot_stride, int frames, size_t n, bool first,

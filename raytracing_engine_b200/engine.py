@@ -36,6 +36,7 @@ EXPORTS = [
     "rtce_trace_accumulate", "rtce_accum_info", "rtce_readback", "rtce_readback_accum",
     "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_flush", "rtce_get_counters",
     "rtce_get_level_counters",
+    "rtce_shade_batch", "rtce_color_info", "rtce_readback_color", "rtce_readback_color_rgba8", "rtce_get_shade_counters",
     "rtce_measure_fp32_issue", "rtce_selftest_math", "rtce_debug_strip_timeline",
     "rtce_debug_launch_timeline",
 ]
@@ -93,6 +94,11 @@ def load_library() -> C.CDLL:
         "rtce_flush": (i32, [vp]),
         "rtce_get_counters": (i32, [vp, C.POINTER(_Counters)]),
         "rtce_get_level_counters": (i32, [vp, i32, C.POINTER(_Counters)]),
+        "rtce_shade_batch": (i32, [vp, vp, i32]),
+        "rtce_color_info": (i32, [vp, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(vp)]),
+        "rtce_readback_color": (i32, [vp, i32, vp]),
+        "rtce_readback_color_rgba8": (i32, [vp, i32, vp]),
+        "rtce_get_shade_counters": (i32, [vp, C.POINTER(C.c_uint64)]),
         "rtce_measure_fp32_issue": (i32, [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "rtce_selftest_math": (i32, [i32, C.POINTER(C.c_uint64)]),
         "rtce_debug_strip_timeline": (i32, [vp, i32, vp, i32]),
@@ -293,6 +299,34 @@ class Engine:
         out = np.empty((h, w), dtype=np.float32)
         self._check(self.lib.rtce_readback_accum(self._ctx, out.ctypes.data, 0), "rtce_readback_accum")
         return out
+
+    # ---- presentation shading pass (fragment.glsl) ----
+    def shade(self, pcs: np.ndarray):
+        """Shade the final level of slots 0..len(pcs)-1 of the latest batch with the batch's push constants."""
+        pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
+        self._check(self.lib.rtce_shade_batch(self._ctx, pcs.ctypes.data, pcs.shape[0]), "rtce_shade_batch")
+
+    def color_info(self, slot: int = 0):
+        w, h, p = C.c_int(), C.c_int(), C.c_void_p()
+        self._check(self.lib.rtce_color_info(self._ctx, slot, C.byref(w), C.byref(h), C.byref(p)), "rtce_color_info")
+        return w.value, h.value, p.value
+
+    def readback_color(self, slot: int = 0) -> np.ndarray:
+        w, h, _ = self.color_info(slot)
+        out = np.empty((h, w, 4), dtype=np.float32)
+        self._check(self.lib.rtce_readback_color(self._ctx, slot, out.ctypes.data), "rtce_readback_color")
+        return out
+
+    def readback_color_rgba8(self, slot: int = 0) -> np.ndarray:
+        w, h, _ = self.color_info(slot)
+        out = np.empty((h, w, 4), dtype=np.uint8)
+        self._check(self.lib.rtce_readback_color_rgba8(self._ctx, slot, out.ctypes.data), "rtce_readback_color_rgba8")
+        return out
+
+    def shade_counters(self) -> dict:
+        o = (C.c_uint64 * 4)()
+        self._check(self.lib.rtce_get_shade_counters(self._ctx, o), "rtce_get_shade_counters")
+        return {"P": int(o[0]), "H": int(o[1]), "D": int(o[2]), "L": int(o[3])}
 
     def render_to_host(self, pcs: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
         """Host push constants in, every frame's final level out to host memory (end-to-end call)."""

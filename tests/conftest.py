@@ -56,3 +56,16 @@ def golden():
 def case_table():
     from cases import cases
     return {c[0]: c for c in cases()}
+
+
+@pytest.fixture(scope="session")
+def shade_golden():
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "shade_golden.json")) as fh:
+        return json.load(fh)
+
+
+@pytest.fixture(scope="session")
+def shade_case_table():
+    from shade_cases import shade_cases
+    return shade_cases()

@@ -286,6 +286,73 @@ def test_accumulate_lanes_equal_single_lane(case_table):
     assert np.array_equal(_bits(a), _bits(b)) and np.array_equal(_bits(a9), _bits(b9))
 
 
+def test_shade_pass_matches_reference_fragment_shader(shade_golden, shade_case_table):
+    """fragment.glsl as a CUDA kernel == the reference's fragment shader compiled as C++ (golden
+    hashes of the RGBA32F and RGBA8 images, counters), window smaller than the level image included."""
+    import hashlib
+    for name, (md, W, H, rot, pos) in shade_case_table.items():
+        g = shade_golden[name]
+        with rt.Engine(0, 1000.0) as e:
+            e.set_option(rt.OPT_COUNTERS, 1)
+            e.set_scene(md)
+            e.set_view(W, H)
+            pcs = rt.make_push_constants([rot], [pos])
+            e.trace(pcs)
+            e.shade(pcs)
+            rgba = e.readback_color(0)
+            assert rgba.shape == (H, W, 4), name
+            assert oracle.sha256(rgba) == g["sha256_rgba32f"], name
+            assert hashlib.sha256(e.readback_color_rgba8(0).tobytes()).hexdigest() == g["sha256_rgba8"], name
+            assert e.shade_counters() == g["counters"], name
+
+
+def test_shade_batch_band_and_frames_in_flight(shade_case_table):
+    """A batch of poses shaded in one call == the checker per frame; a row band shades only its rows; with
+    frames in flight the pass reads the window of the latest batch."""
+    o = oracle.best()
+    port = oracle.load("port")
+    md, W, H, _, _ = shade_case_table["default_800x600"]
+    rots, poss = camera.bench_camera_path(12)
+    pcs = rt.make_push_constants(rots, poss)
+    want = {}
+    for k in (0, 5, 11):
+        lv, _ = o.trace(scene.spheres_of(md), [W, H], scene.view_ratio(W, H), rots[k], poss[k], 1000.0, 0)
+        want[k], _ = port.shade(md, [W, H], scene.view_ratio(W, H), rots[k], poss[k], lv[-1])
+    with rt.Engine(0, 1000.0) as e:
+        e.set_option(rt.OPT_FRAME_SLOTS, 6)
+        e.set_scene(md)
+        e.set_view(W, H)
+        e.set_option(rt.OPT_FRAMES_IN_FLIGHT, 3)
+        e.trace(pcs[0:6])
+        e.trace(pcs[6:12])            # second lane, second window
+        e.shade(pcs[6:12])
+        assert np.array_equal(_bits(e.readback_color(5)), _bits(want[11]))
+        e.set_option(rt.OPT_FRAMES_IN_FLIGHT, 1)
+        e.trace(pcs[0:6])
+        e.shade(pcs[0:6])
+        assert np.array_equal(_bits(e.readback_color(0)), _bits(want[0]))
+        assert np.array_equal(_bits(e.readback_color(5)), _bits(want[5]))
+    with rt.Engine(0, 1000.0) as e:
+        e.set_scene(md)
+        e.set_view(W, H)
+        e.set_rect(0, 296, W, 456)
+        e.trace(pcs[5:6])
+        e.shade(pcs[5:6])
+        part = e.readback_color(0)
+        assert np.array_equal(_bits(part[296:456]), _bits(want[5][296:456]))
+        assert not part[:296].any() and not part[456:].any()
+
+
+def test_shade_needs_materials_and_lights():
+    with rt.Engine(0, 1000.0) as e:
+        e.set_spheres(scene.spheres_of(scene.default_mutable_data()))   # no materials / lights
+        e.set_view(320, 200)
+        pcs = rt.make_push_constants([camera.IDENTITY_ROT], [[0, 0, 0]])
+        e.trace(pcs)
+        with pytest.raises(rt.RtceError):
+            e.shade(pcs)
+
+
 def test_large_scene_kernel_matches_checker():
     """objCount > 8 (CTA-per-ray kernel) on a bigger synthetic scene than the golden cases."""
     o = oracle.best()
