@@ -3,9 +3,11 @@
 // per-ray x per-object cache of lower bounds (`float distances[MAX_OBJECTS]`, compute.glsl:35)
 // fits on chip: ONE CTA marches ONE ray at a time and the objects are spread over its threads.
 //
-//   * distances[] lives in shared memory (n floats), each thread owns objects tid, tid+T, ...
-//   * per march step every thread updates its objects (3 FP32 ops each; the exact SDF only when
-//     the bound falls inside the cone radius) and the block takes min over all of them.
+//   * distances[] lives in shared memory as groups of four (one 128-bit access per group), each
+//     thread owns groups tid, tid+T, ...
+//   * per march step every thread updates its objects (one subtract and one min each, one compare
+//     per group; the exact SDF only when a bound falls inside the cone radius) and the block takes
+//     min over all of them.
 //     min is exactly associative and commutative on non-NaN floats, so the reduction order
 //     cannot change a bit.
 //   * the scalar ray state (len, last, position) is computed redundantly by every thread with
@@ -33,9 +35,10 @@ RTCE_DEV float block_min(float v, float* red /* [2][8] */, int parity) {
 template <bool COUNT>
 __global__ void __launch_bounds__(kLargeThreads)
     k_trace_level_large(const __grid_constant__ LevelParamsLarge P, long long total_rays) {
-    extern __shared__ float s_dist[];   // n floats
+    extern __shared__ float4 s_dist4[];   // ceil(n / 4) groups of four lower bounds
     __shared__ float s_red[16];
     const int n = P.n_spheres;
+    const int n4 = (n + 3) >> 2;
     const int rw = P.x1 - P.x0, rh = P.y1 - P.y0;
     const long long per_frame = (long long)rw * rh;
     unsigned long long cE = 0, cS = 0, cR = 0;
@@ -58,10 +61,20 @@ __global__ void __launch_bounds__(kLargeThreads)
         const float oy = fadd(cam.pos[1], fmul(dir.y, start));
         const float oz = fadd(cam.pos[2], fmul(dir.z, start));
 
-        // traceCone :37-39
-        for (int i = threadIdx.x; i < n; i += kLargeThreads) {
-            const float4 s = __ldg(P.spheres + i);
-            s_dist[i] = sphere_sdf(ox, oy, oz, s.x, s.y, s.z, s.w);
+        // traceCone :37-39; distances[] is kept as float4 groups (slots past n hold +inf: never refreshed,
+        // never the minimum)
+        for (int i4 = threadIdx.x; i4 < n4; i4 += kLargeThreads) {
+            float v[4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                const int i = 4 * i4 + c;
+                v[c] = __int_as_float(0x7F800000);
+                if (i < n) {
+                    const float4 s = __ldg(P.spheres + i);
+                    v[c] = sphere_sdf(ox, oy, oz, s.x, s.y, s.z, s.w);
+                }
+            }
+            s_dist4[i4] = make_float4(v[0], v[1], v[2], v[3]);
         }
         if (COUNT && threadIdx.x == 0) cE += (unsigned long long)n;
         float len = 0.0f, last = 0.0f;
@@ -71,15 +84,30 @@ __global__ void __launch_bounds__(kLargeThreads)
             const float pz = fadd(oz, fmul(dir.z, len));
             const float radius = fmul(fadd(len, 1.0f), P.threshold);
             float m = P.render_dist;   // :49
-            for (int i = threadIdx.x; i < n; i += kLargeThreads) {   // :51-57 (each thread touches only its own slots)
-                float d = fsub(s_dist[i], last);
-                if (d <= radius) {
-                    const float4 s = __ldg(P.spheres + i);
-                    d = sphere_sdf(px, py, pz, s.x, s.y, s.z, s.w);
-                    if (COUNT) cE++;
+            // :51-57, four objects per shared-memory access (each thread touches only its own groups): per object
+            // one subtract and one min, plus one compare per group; the exact SDF only inside the cone radius
+            for (int i4 = threadIdx.x; i4 < n4; i4 += kLargeThreads) {
+                float4 d = s_dist4[i4];
+                d.x = fsub(d.x, last);
+                d.y = fsub(d.y, last);
+                d.z = fsub(d.z, last);
+                d.w = fsub(d.w, last);
+                float m4 = fminf(fminf(d.x, d.y), fminf(d.z, d.w));
+                if (m4 <= radius) {
+                    float v[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+                    for (int c = 0; c < 4; c++) {
+                        if (v[c] <= radius) {   // never true for the +inf padding
+                            const float4 s = __ldg(P.spheres + 4 * i4 + c);
+                            v[c] = sphere_sdf(px, py, pz, s.x, s.y, s.z, s.w);
+                            if (COUNT) cE++;
+                        }
+                    }
+                    d = make_float4(v[0], v[1], v[2], v[3]);
+                    m4 = fminf(fminf(d.x, d.y), fminf(d.z, d.w));
                 }
-                s_dist[i] = d;
-                m = fminf(m, d);
+                s_dist4[i4] = d;
+                m = fminf(m, m4);
             }
             const float dist = block_min(m, s_red, parity);
             parity ^= 1;
@@ -111,7 +139,7 @@ __global__ void __launch_bounds__(kLargeThreads)
 cudaError_t launch_trace_level_large(const LevelParamsLarge& p, int frames, bool count, cudaStream_t st) {
     if (p.x1 <= p.x0 || p.y1 <= p.y0 || frames <= 0) return cudaSuccess;
     const long long total = (long long)(p.x1 - p.x0) * (p.y1 - p.y0) * frames;
-    const size_t smem = sizeof(float) * (size_t)p.n_spheres;
+    const size_t smem = sizeof(float4) * (size_t)((p.n_spheres + 3) / 4);
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

@@ -24,8 +24,8 @@ RTCE_DEV V3 v_sub(V3 a, V3 b) { return {fsub(a.x, b.x), fsub(a.y, b.y), fsub(a.z
 RTCE_DEV V3 v_neg(V3 a) { return {-a.x, -a.y, -a.z}; }
 RTCE_DEV float v_dot(V3 a, V3 b) { return fadd(fadd(fmul(a.x, b.x), fmul(a.y, b.y)), fmul(a.z, b.z)); }
 RTCE_DEV float v_length(V3 a) { return sqrt_fast(v_dot(a, a)); }
-RTCE_DEV V3 v_normalize(V3 a) {   // v * (1.0 / length(v))
-    const float inv = __frcp_rn(v_length(a));
+RTCE_DEV V3 v_normalize(V3 a) {   // v * (1.0 / length(v)); rcp_fast is exact for 2^-126 <= length <= 2^126
+    const float inv = rcp_fast(v_length(a));
     return {fmul(a.x, inv), fmul(a.y, inv), fmul(a.z, inv)};
 }
 RTCE_DEV V3 xyz(float4 v) { return {v.x, v.y, v.z}; }
@@ -33,29 +33,32 @@ RTCE_DEV V3 xyz(float4 v) { return {v.x, v.y, v.z}; }
 // utilities.glsl:36-38
 RTCE_DEV float sdf(V3 p, float4 s) { return fsub(v_length(v_sub(p, xyz(s))), s.w); }
 
-// fragment.glsl:89-121
-template <bool COUNT>
+// fragment.glsl:89-121.  The refresh of :107-109 is evaluated under a warp-level vote and selected per lane
+// (no per-lane branch per object and trip); the values are those of the branchy form.
+template <int N, bool COUNT>
 RTCE_DEV float shadow_ray(const ShadeParams& P, V3 origin, V3 step, float end, unsigned& cD) {
     const float RAY_RADIUS = 0.01f;
-    float d[kSmallSceneMax];
+    float d[N];
 #pragma unroll
-    for (int i = 0; i < kSmallSceneMax; i++)
-        if (i < P.n_obj) d[i] = sdf(origin, P.obj[i]);   // :92-94
-    if (COUNT) cD += (unsigned)P.n_obj;
+    for (int i = 0; i < N; i++) d[i] = sdf(origin, P.obj[i]);   // :92-94
+    if (COUNT) cD += (unsigned)N;
     float last = 0.0f, nearest = 1.0f;
     for (float len = 0.0f; len < end; len = fadd(len, fadd(last, RAY_RADIUS))) {   // :99
         const V3 pos = {fadd(origin.x, fmul(step.x, len)), fadd(origin.y, fmul(step.y, len)), fadd(origin.z, fmul(step.z, len))};
         float dist = end;   // :104
 #pragma unroll
-        for (int i = 0; i < kSmallSceneMax; i++) {   // :105-111
-            if (i < P.n_obj) {
-                d[i] = fsub(d[i], last);
-                if (d[i] <= nearest) {
-                    d[i] = sdf(pos, P.obj[i]);
-                    if (COUNT) cD++;
-                }
-                dist = lit_min(dist, d[i]);
+        for (int i = 0; i < N; i++) {   // :105-111
+            const float bound = fsub(d[i], last);
+            const bool refresh = bound <= nearest;
+            if (COUNT) cD += refresh ? 1u : 0u;
+            d[i] = bound;
+            // skipped when no lane marching with this one needs it (the far spheres, most trips); a lane
+            // that does need it always sees its own vote
+            if (__any_sync(__activemask(), refresh)) {
+                const float exact = sdf(pos, P.obj[i]);
+                d[i] = refresh ? exact : bound;
             }
+            dist = lit_min(dist, d[i]);
         }
         if (dist <= RAY_RADIUS) return 0.0f;   // :113-115
         last = lit_max(dist, 0.0f);
@@ -64,7 +67,7 @@ RTCE_DEV float shadow_ray(const ShadeParams& P, V3 origin, V3 step, float end, u
     return nearest;
 }
 
-template <bool COUNT>
+template <int N, bool COUNT>
 __global__ void __launch_bounds__(256)
     k_shade(const __grid_constant__ ShadeParams P) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -75,35 +78,33 @@ __global__ void __launch_bounds__(256)
     if (x < P.x1 && y < P.y1) {
         cP = 1;
         const float CAM_FALL_OFF = 0.01f, LIGHT_FALL_OFF = 0.01f;
-        const float4 q = __ldg(reinterpret_cast<const float4*>(P.cams + f));
-        const float4 t = __ldg(reinterpret_cast<const float4*>(P.cams + f) + 1);
-        const V3 cam = {t.x, t.y, t.z};
-        // gl_FragCoord.xy = pixel centre; :126-130
-        const float fx = fadd((float)x, 0.5f), fy = fadd((float)y, 0.5f);
-        const float ncx = fmul(fsub(__fdiv_rn(fmul(fx, 2.0f), P.vw), 1.0f), P.ratx);
-        const float ncy = fmul(fsub(__fdiv_rn(fmul(fy, 2.0f), P.vh), 1.0f), P.raty);
-        const Vec3 rv = rotate_q(q.x, q.y, q.z, q.w, ncx, 1.0f, ncy);
-        const V3 step = v_normalize({rv.x, rv.y, rv.z});
         const size_t px = (size_t)y * (size_t)P.w + (size_t)x;
         const float total = __ldg(P.depth + (size_t)f * P.depth_stride + px);   // :132
         float r = 0.0f, g = 0.0f, b = 0.0f;
-        if (!(total >= P.render_dist)) {   // :134-137
+        if (!(total >= P.render_dist)) {   // :134-137 (a background fragment needs no view direction)
+            const float4 q = __ldg(reinterpret_cast<const float4*>(P.cams + f));
+            const float4 t = __ldg(reinterpret_cast<const float4*>(P.cams + f) + 1);
+            const V3 cam = {t.x, t.y, t.z};
+            // gl_FragCoord.xy = pixel centre; :126-130
+            const float fx = fadd((float)x, 0.5f), fy = fadd((float)y, 0.5f);
+            const float ncx = fmul(fsub(__fdiv_rn(fmul(fx, 2.0f), P.vw), 1.0f), P.ratx);
+            const float ncy = fmul(fsub(__fdiv_rn(fmul(fy, 2.0f), P.vh), 1.0f), P.raty);
+            const Vec3 rv = rotate_q(q.x, q.y, q.z, q.w, ncx, 1.0f, ncy);
+            const V3 step = v_normalize({rv.x, rv.y, rv.z});
             cH = 1;
             const V3 position = {fadd(cam.x, fmul(step.x, total)), fadd(cam.y, fmul(step.y, total)), fadd(cam.z, fmul(step.z, total))};
             // nearest object and its material, :141-153
             int best = 0;
             float dist = sdf(position, P.obj[0]);
 #pragma unroll
-            for (int i = 1; i < kSmallSceneMax; i++) {
-                if (i < P.n_obj) {
-                    const float nd = sdf(position, P.obj[i]);
-                    if (nd < dist) {
-                        dist = nd;
-                        best = i;
-                    }
+            for (int i = 1; i < N; i++) {
+                const float nd = sdf(position, P.obj[i]);
+                if (nd < dist) {
+                    dist = nd;
+                    best = i;
                 }
             }
-            if (COUNT) cD += (unsigned)P.n_obj + 1u;
+            if (COUNT) cD += (unsigned)N + 1u;
             const float4 object = P.obj[best];
             const float4 matc = P.matc[best];   // color.xyz, shine
             const float ambient = P.amb[best];
@@ -119,7 +120,7 @@ __global__ void __launch_bounds__(256)
                 const float ldist = v_length(v_sub(position, lpos));   // :171
                 if (COUNT) { cD++; cL++; }
                 const V3 so = {fadd(position.x, ldir.x), fadd(position.y, ldir.y), fadd(position.z, ldir.z)};
-                const float soft = lit_min(shadow_ray<COUNT>(P, so, ldir, ldist, cD), 1.0f);   // :173
+                const float soft = lit_min(shadow_ray<N, COUNT>(P, so, ldir, ldist, cD), 1.0f);   // :173
                 const float lfall = lit_max(fmul(fmul(LIGHT_FALL_OFF, ldist), ldist), 1.0f);   // :175
                 const float diff = lit_max(v_dot(normal, ldir), 0.0f);   // :177
                 const V3 inc = v_neg(ldir);   // :178, reflect(-lightDir, normal)
@@ -165,15 +166,30 @@ __global__ void k_rgba8(const float4* __restrict__ in, uchar4* __restrict__ out,
 
 }  // namespace
 
+template <int N>
+static cudaError_t launch_shade_n(const ShadeParams& p, dim3 grid, bool count, cudaStream_t st) {
+    if (count)
+        k_shade<N, true><<<grid, 256, 0, st>>>(p);
+    else
+        k_shade<N, false><<<grid, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_shade(const ShadeParams& p, int frames, bool count, cudaStream_t st) {
     if (p.x1 <= p.x0 || p.y1 <= p.y0 || frames <= 0) return cudaSuccess;
     if (p.n_obj < 1 || p.n_obj > kSmallSceneMax || p.n_light < 0 || p.n_light > kSmallSceneMax || !p.cams) return cudaErrorInvalidValue;
     dim3 grid((unsigned)((p.x1 - p.x0 + 31) / 32), (unsigned)((p.y1 - p.y0 + 7) / 8), (unsigned)frames);
-    if (count)
-        k_shade<true><<<grid, 256, 0, st>>>(p);
-    else
-        k_shade<false><<<grid, 256, 0, st>>>(p);
-    return cudaGetLastError();
+    switch (p.n_obj) {
+        case 1: return launch_shade_n<1>(p, grid, count, st);
+        case 2: return launch_shade_n<2>(p, grid, count, st);
+        case 3: return launch_shade_n<3>(p, grid, count, st);
+        case 4: return launch_shade_n<4>(p, grid, count, st);
+        case 5: return launch_shade_n<5>(p, grid, count, st);
+        case 6: return launch_shade_n<6>(p, grid, count, st);
+        case 7: return launch_shade_n<7>(p, grid, count, st);
+        case 8: return launch_shade_n<8>(p, grid, count, st);
+        default: return cudaErrorInvalidValue;
+    }
 }
 
 cudaError_t launch_rgba8(const float4* in, uchar4* out, size_t n, cudaStream_t st) {
