@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS))
     ap.add_argument("--in-flight", type=int, default=None,
-                    help="RTCE_OPT_FRAMES_IN_FLIGHT for frame-by-frame workloads (default 4): batches of consecutive steps "
+                    help="RTCE_OPT_FRAMES_IN_FLIGHT for frame-by-frame workloads (default 6): batches of consecutive steps "
                          "rotate over this many windows of frame slots and overlap on the device; 1 = strict stream order")
     ap.add_argument("--strip-ctas", type=int, default=None, help="RTCE_OPT_STRIP_CTAS_PER_SM")
     ap.add_argument("--graph", type=int, default=None, help="RTCE_OPT_GRAPH: 1 = replay the launch chain from a CUDA graph (default), 0 = issue every launch")
@@ -262,7 +262,7 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_GRAPH, args.graph)
     if args.strip_ctas is not None:
         eng.set_option(rt.OPT_STRIP_CTAS_PER_SM, args.strip_ctas)
-    in_flight = 1 if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 4)
+    in_flight = (args.in_flight or 1) if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 6)
     eng.set_option(rt.OPT_FRAMES_IN_FLIGHT, in_flight)
     slots = min(frames_rank, 16)
     eng.set_option(rt.OPT_FRAME_SLOTS, slots)
@@ -527,7 +527,7 @@ def run_ours(args, wl):
                                    "fixed work per GPU), whole image per frame, results stay in each rank's HBM; no data-path "
                                    "collective (frames are independent units)" if weak else
                                    f"{n_gpus} row bands of the final level + one NCCL gather of the accumulated image to rank 0 per step"),
-                   "frames_in_flight": in_flight if not wl["accumulate"] else "3 chunks (internal to rtce_trace_accumulate)",
+                   "frames_in_flight": in_flight if not wl["accumulate"] else f"{max(in_flight, 4)} chunks (internal to rtce_trace_accumulate)",
                    "l2": f"no flush: each step rewrites {bytes_step / 1e6:.0f} MB of pyramid (> 126 MB L2 when frames >= 12 at 1080p); parents are meant to be L2 hits",
                    "kernel": {0: "auto (strip kernel + overflow launch per fine level, one per-pixel launch per coarse level)", 1: "per-level", 2: "fused", 3: "strip kernel + overflow launch per fine level, one per-pixel launch per coarse level"}[args.kernel]},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps) * n_gpus,

@@ -108,8 +108,13 @@ typedef enum rtce_option {
                                    batch whose window the next call reuses; rtce_flush (stream-level) or rtce_sync /
                                    rtce_readback* (host-level) order it after everything.  rtce_level_info and
                                    rtce_readback address the window of the latest call.  W = 1 is strict stream order. */
-    RTCE_OPT_STRIP_CTAS_PER_SM = 10, /* kernel plan 3: persistent CTAs per SM of a strip launch; 0 (default) = every resident
-                                   slot (3 on B200).  Fewer leave room for the launches of other lanes in flight. */
+    RTCE_OPT_STRIP_CTAS_PER_SM = 10, /* kernel plan 3: persistent CTAs per SM of a strip launch; 0 (default) = auto: every
+                                   resident slot (3 on B200) in strict stream order, 2 with two or three lanes in flight, 1 with more
+                                   (leaves room for the launches of the other lanes). */
+    RTCE_OPT_FAR_MISS = 11,     /* kernel plan 3: 1 (default) = a ray whose parent texel lies beyond every sphere by more than
+                                   RENDER_DIST (host-side conservative bound per camera) is resolved as start + RENDER_DIST
+                                   without evaluating an SDF: exactly what compute.glsl:37-66 computes for it (all
+                                   distances[i] >= RENDER_DIST -> one trip, no hit).  0 = evaluate every ray in full. */
     RTCE_OPT_GRAPH = 8,         /* kernel plan 3: 1 (default) = the launch chain of a frame batch (every level of every group,
                                    forks and joins included) is captured once into a CUDA graph and replayed by later
                                    calls with the same batch shape; the per-call cameras travel through device memory.
@@ -163,7 +168,7 @@ int rtce_trace(rtce_ctx* ctx, const rtce_push_constants* pc);
 int rtce_trace_batch(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
 /* Extension ("progressive accumulation"): trace `frames` frames and keep only the
  * running FP32 sum of their final levels, divided by `frames` at the end, in an internal image.
- * Up to three chunks of frames are traced side by side (own streams, own windows of slots); the sum
+ * Up to four chunks of frames are traced side by side (own streams, own windows of slots); the sum
  * is taken on the context's stream in frame order. */
 int rtce_trace_accumulate(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
 int rtce_accum_info(const rtce_ctx* ctx, int* w, int* h, float** device_ptr);

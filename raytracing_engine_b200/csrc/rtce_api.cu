@@ -7,6 +7,7 @@
 #include <cstdio>
 #include <cstring>
 #include <new>
+#include <limits>
 #include <string>
 #include <vector>
 
@@ -27,7 +28,7 @@ static constexpr unsigned kOverflowCap = 1u << 19;   // rays per frame group (38
 // level of another — and rtce_trace_accumulate rotates its chunks the same way.
 static constexpr int kMaxLanes = 8;
 static constexpr int kCamRing = 8;
-struct ChunkGraph { int frames, slot0; bool own_stream; uint64_t version; cudaGraphExec_t exec; uint64_t launches; };
+struct ChunkGraph { int frames, slot0, lanes; uint64_t version; cudaGraphExec_t exec; uint64_t launches; };   // lanes: 0 = strict order
 struct Lane {
     bool ready = false;
     bool pending = false;                  // traced since the context's stream last waited for it
@@ -57,6 +58,7 @@ struct rtce_ctx {
     int coarse_mode = 0;                 // RTCE_OPT_COARSE_FUSED: 0 one launch per level, 1 fused-pyramid kernel, 2 cluster kernel
     int strip_rows = 16;                 // RTCE_OPT_STRIP_ROWS
     int strip_ctas_per_sm = 0;           // RTCE_OPT_STRIP_CTAS_PER_SM (0 = every resident slot)
+    bool far_cull = true;                // RTCE_OPT_FAR_MISS: resolve rays that start beyond every sphere without SDFs
     // diagnostics (rtce_debug_launch_timeline): an event pair around every kernel launch
     struct LaunchMark { cudaEvent_t e0, e1; int kind, level, group; };
     bool mark_launches = false;
@@ -113,6 +115,7 @@ struct rtce_ctx {
     Lane lanes[kMaxLanes];
     int in_flight = 1;                     // RTCE_OPT_FRAMES_IN_FLIGHT
     int next_lane = 0, last_lane = 0;
+    int lanes_active = 1;                  // lanes the current call rotates over
     int windows_alloc = 0;                 // slot windows the pyramid allocation holds
     cudaEvent_t ev_user = nullptr;         // "everything the caller enqueued so far" on `stream`
     uint64_t launches = 0;
@@ -356,6 +359,7 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             if (value < 1 || value > kStripMaxRows) return fail(c, RTCE_ERR_INVALID, "strip rows out of range");
             c->strip_rows = (int)value;
             return RTCE_OK;
+        case RTCE_OPT_FAR_MISS: c->far_cull = value != 0; return RTCE_OK;
         case RTCE_OPT_STRIP_CTAS_PER_SM:
             if (value < 0 || value > 8) return fail(c, RTCE_ERR_INVALID, "strip CTAs per SM out of range");
             c->strip_ctas_per_sm = (int)value;

@@ -152,18 +152,24 @@ __global__ void __launch_bounds__(256)
             const float4 q = __ldg(reinterpret_cast<const float4*>(P.cams + f));
             const float4 t = __ldg(reinterpret_cast<const float4*>(P.cams + f) + 1);
             cam.rot[0] = q.x; cam.rot[1] = q.y; cam.rot[2] = q.z; cam.rot[3] = q.w;
-            cam.pos[0] = t.x; cam.pos[1] = t.y; cam.pos[2] = t.z; cam.pad = 0.0f;
+            cam.pos[0] = t.x; cam.pos[1] = t.y; cam.pos[2] = t.z; cam.pad = t.w;   // pad = far-miss distance
         }
-        const float4 col = col_terms(cam, norm_coord(x, P.isx, P.ratx));
-        const float4 row = row_terms(cam, norm_coord(y, P.isy, P.raty));
         float start = 1.0f;   // compute.glsl:79
         if (P.iter > 0) start = __ldg(P.parent + (size_t)f * P.slot_stride + (size_t)(y >> 1) * (size_t)P.pw + (size_t)(x >> 1));
-        Ray<N> ray;
-        ray_setup<N>(ray, col, row, start, cam, P.sph);
-        float len = 0.0f;
-        bool go = first_step<N, COUNT>(ray, len, P.threshold, P.render_dist, cE, cS);
-        float last = len;
-        while (go) go = march_block_pred<N, COUNT, RTCE_PRED_BLOCK>(ray, len, last, P.threshold, P.render_dist, P.sph, cE, cS);
+        float len = P.render_dist;
+        if (P.iter > 0 && start >= cam.pad) {
+            // beyond every sphere by more than RENDER_DIST: one trip with dist = RENDER_DIST, no hit (see strip kernel)
+            if (COUNT) { cE += (unsigned)N; cS++; }
+        } else {
+            const float4 col = col_terms(cam, norm_coord(x, P.isx, P.ratx));
+            const float4 row = row_terms(cam, norm_coord(y, P.isy, P.raty));
+            Ray<N> ray;
+            ray_setup<N>(ray, col, row, start, cam, P.sph);
+            len = 0.0f;
+            bool go = first_step<N, COUNT>(ray, len, P.threshold, P.render_dist, cE, cS);
+            float last = len;
+            while (go) go = march_block_pred<N, COUNT, RTCE_PRED_BLOCK>(ray, len, last, P.threshold, P.render_dist, P.sph, cE, cS);
+        }
         P.out[(size_t)f * P.slot_stride + (size_t)y * (size_t)P.w + (size_t)x] = glsl_max(fadd(start, len), 0.0f);   // :84, :86
         cR = 1;
     }

@@ -34,6 +34,7 @@ constexpr int kPinWords = 40;       // per-warp scratch for pinning uniforms (>=
 #ifndef RTCE_TAIL_BUDGET
 #define RTCE_TAIL_BUDGET (1 << 30)
 #endif
+constexpr int kFarPairs = 8;        // parent rows of a task the far-miss fast path handles (16 rows per task)
 constexpr int kMaxAge = RTCE_MAX_AGE;   // tail trips after which a ray is evicted to the overflow queue
 constexpr int kTailBudget = RTCE_TAIL_BUDGET;   // tail trips a warp spends on ONE task before it evicts every tail ray it
                                                 // holds: a tile whose rays all need ~6 trips would otherwise keep one
@@ -179,6 +180,12 @@ RTCE_DEV int tail_march(float* q, int qn, const bool drain, float* __restrict__ 
 #ifndef RTCE_OQ_PER_WARP
 #define RTCE_OQ_PER_WARP 32
 #endif
+#ifndef RTCE_OQ_BRANCHY
+#define RTCE_OQ_BRANCHY 0
+#endif
+#ifndef RTCE_OQ_REFILL
+#define RTCE_OQ_REFILL kRefillMin
+#endif
 template <int N, bool COUNT>
 __global__ void __launch_bounds__(128)
     k_march_overflow(const __grid_constant__ OverflowParams P) {
@@ -202,7 +209,7 @@ __global__ void __launch_bounds__(128)
     for (;;) {
         const unsigned am = __ballot_sync(RTCE_FULL, active);
         const int nfree = 32 - __popc(am);
-        if (!exhausted && nfree >= kRefillMin) {
+        if (!exhausted && nfree >= RTCE_OQ_REFILL) {
             unsigned base = 0;
             if (lane == 0) base = atomicAdd(P.oq_head, (unsigned)nfree);
             base = __shfl_sync(RTCE_FULL, base, 0);
@@ -218,7 +225,11 @@ __global__ void __launch_bounds__(128)
         }
         if (active) {
             unsigned e = 0, s = 0;
+#if RTCE_OQ_BRANCHY
+            const bool go = march_step<N, COUNT>(r, len, last, thr, rd, sph, e, s);
+#else
             const bool go = march_block_pred<N, COUNT, RTCE_PRED_BLOCK>(r, len, last, thr, rd, sph, e, s);
+#endif
             if (COUNT) { cE += e; cS += s; }
             if (!go) {
                 img[off] = glsl_max(fadd(start, len), 0.0f);   // compute.glsl:84, :86
@@ -347,6 +358,30 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
                 ticket = __shfl_sync(RTCE_FULL, next, 0);
                 continue;
             }
+            // Cold pass, whole task a far miss (most of the background): every parent texel of the task is at
+            // least the camera's far-miss distance away, so every ray is start + RENDER_DIST (see the row loop).
+            // All parent rows are fetched at once — row by row this path would be a chain of dependent loads.
+            if (second && !(yb & 1) && pairs_left < kFarPairs) {
+                const float tf = __ldg(reinterpret_cast<const float*>(P.cams + f) + 7);
+                float pv[kFarPairs];
+#pragma unroll
+                for (int k = 0; k < kFarPairs; k++) pv[k] = k <= pairs_left ? __ldg(pp + (size_t)k * P.pw) : pv[0];
+                float nearest = pv[0];
+#pragma unroll
+                for (int k = 1; k < kFarPairs; k++) nearest = fminf(nearest, pv[k]);
+                if (__all_sync(RTCE_FULL, !xok || nearest >= tf)) {
+                    if (xok) {
+                        float* o = img + ((size_t)f * P.slot_stride + (size_t)yb * P.w + xc);
+#pragma unroll
+                        for (int rr = 0; rr < 2 * kFarPairs; rr++)
+                            if (rr < rows) o[(size_t)rr * P.w] = fadd(pv[rr >> 1], rd);   // :84, :86 (positive)
+                        if (COUNT) { cR += (unsigned)rows; cE += (unsigned)(N * rows); cS += (unsigned)rows; }
+                    }
+                    ndone++;
+                    ticket = __shfl_sync(RTCE_FULL, next, 0);
+                    continue;
+                }
+            }
             if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
         }
         ndone++;
@@ -359,14 +394,26 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
             for (int i = 0; i < 4; i++) cam.rot[i] = pin[i];
 #pragma unroll
             for (int i = 0; i < 3; i++) cam.pos[i] = pin[4 + i];
-            cam.pad = 0.0f;
+            cam.pad = pin[7];   // far-miss distance of this camera (host: far_miss_distance)
         }
+        const float tfar = cam.pad;
         const float4 col = col_terms(cam, norm_coord(xc, P.isx, P.ratx));
         __syncwarp();   // the previous task's table reads are done
         if (lane < rows) rowtab[lane] = row_terms(cam, norm_coord(yb + lane, P.isy, P.raty));
         __syncwarp();
         float* op = img + ((size_t)f * P.slot_stride + (size_t)yb * P.w + xc);   // this lane's texel, row by row
         for (int rr = 0; rr < rows; rr++, op += P.w) {
+            if (HAS_PARENT && __all_sync(RTCE_FULL, !xok || start >= tfar)) {
+                // every ray of the row starts beyond every sphere by more than RENDER_DIST: all distances[i] >=
+                // RENDER_DIST, so the first trip takes dist = RENDER_DIST, is no hit and ends the march (:44-66)
+                if (xok) *op = fadd(start, rd);   // :84, :86 (positive)
+                if (COUNT && xok) { cR++; cE += (unsigned)N; cS++; }
+                if ((yb + rr) & 1) {   // next row starts a new pair
+                    start = ahead;
+                    if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
+                }
+                continue;
+            }
             const float4 row = rowtab[rr];
             Ray<N> ray;
             ray_setup<N>(ray, col, row, start, cam, sph);

@@ -20,6 +20,7 @@ OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS, OPT_C
 OPT_GRAPH = 8
 OPT_FRAMES_IN_FLIGHT = 9
 OPT_STRIP_CTAS_PER_SM = 10
+OPT_FAR_MISS = 11
 KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED, KERNEL_STRIP = 0, 1, 2, 3
 
 # compute.glsl:7-12 PushConstantData, 40 bytes

@@ -101,6 +101,39 @@ def test_fuzz_against_cpu_checker(mode):
             assert {k: c[k] for k in "RES"} == cnt
 
 
+@pytest.mark.parametrize("far_miss", [1, 0])
+def test_far_miss_shortcut_is_exact(far_miss):
+    """RTCE_OPT_FAR_MISS: rays resolved as start + RENDER_DIST without an SDF == the full evaluation == the checker,
+    with spheres near the far-miss bound, beyond RENDER_DIST, behind the camera, huge coordinates, no spheres."""
+    o = oracle.best()
+    rs = np.random.RandomState(99)
+    scenes = []
+    for scale in (1.0, 60.0, 300.0, 2000.0, 1.0e5):
+        n = int(rs.randint(1, 9))
+        sph = np.zeros((n, 4), np.float32)
+        sph[:, :3] = rs.uniform(-10, 10, (n, 3)) * scale
+        sph[:, 3] = rs.uniform(0.2, 3.0, n) * min(scale, 400.0)
+        scenes.append(sph)
+    scenes.append(np.zeros((0, 4), np.float32))
+    for k, sph in enumerate(scenes):
+        W, H = 200 + 8 * k, 120 + 3 * k
+        rot = camera.rotation(0.3 * k, 0.1 * k - 0.2)
+        pos = (rs.uniform(-5, 5, 3) * (1.0 if k % 2 else 50.0)).astype(np.float32)
+        ref, cnt = o.trace(sph, [W, H], scene.view_ratio(W, H), rot, pos, 1000.0, 0)
+        for mode in ((rt.KERNEL_STRIP, 0), (rt.KERNEL_AUTO, None)):
+            with rt.Engine(0, 1000.0) as e:
+                _set_mode(e, mode)
+                e.set_option(rt.OPT_FAR_MISS, far_miss)
+                e.set_option(rt.OPT_COUNTERS, 1)
+                e.set_spheres(sph)
+                e.set_view(W, H)
+                e.trace(rt.make_push_constants([rot], [pos]))
+                for i, (a, b) in enumerate(zip(e.readback_all_levels(), ref)):
+                    assert np.array_equal(_bits(a), _bits(b)), (k, mode, i)
+                c = e.counters()
+                assert {q: c[q] for q in "RES"} == cnt, (k, mode)
+
+
 def test_render_dist_parameter():
     """RENDER_DIST is a specialization constant (compute.glsl:32); other values via the C port."""
     o = oracle.load("port")
