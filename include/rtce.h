@@ -207,6 +207,10 @@ int rtce_get_counters(rtce_ctx* ctx, rtce_counters* out);
 /* The same per pyramid level (negative = from the last).  A fused-pyramid launch books all the levels it
  * traces under its finest one. */
 int rtce_get_level_counters(rtce_ctx* ctx, int level, rtce_counters* out);
+/* Rays of the last counted call that the far-miss shortcut (RTCE_OPT_FAR_MISS) resolved without an SDF: of pyramid
+ * level `level`, or of every level when level < 0.  They are included in rtce_counters with the work the reference
+ * algorithm does for them (1 trip, objCount evaluations). */
+int rtce_get_far_miss_rays(rtce_ctx* ctx, int level, uint64_t* out);
 
 /* -- measurement support (no reference counterpart) ---------------------------------------------
  * Sustained FP32 CUDA-core issue rate of `device`: a register-only kernel of independent,

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(256)
     const int x = P.x0 + blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
     const int y = P.y0 + blockIdx.y * 8 + (warp >> 2) * 4 + (lane >> 3);
     const int f = blockIdx.z;
-    unsigned cR = 0, cE = 0, cS = 0;
+    unsigned cR = 0, cE = 0, cS = 0, cF = 0;
     if (x < P.x1 && y < P.y1) {
         Cam cam;
         {
@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(256)
         float len = P.render_dist;
         if (P.iter > 0 && start >= cam.pad) {
             // beyond every sphere by more than RENDER_DIST: one trip with dist = RENDER_DIST, no hit (see strip kernel)
-            if (COUNT) { cE += (unsigned)N; cS++; }
+            if (COUNT) { cE += (unsigned)N; cS++; cF = 1; }
         } else {
             const float4 col = col_terms(cam, norm_coord(x, P.isx, P.ratx));
             const float4 row = row_terms(cam, norm_coord(y, P.isy, P.raty));
@@ -178,11 +178,13 @@ __global__ void __launch_bounds__(256)
             cR += __shfl_down_sync(0xffffffffu, cR, o);
             cE += __shfl_down_sync(0xffffffffu, cE, o);
             cS += __shfl_down_sync(0xffffffffu, cS, o);
+            cF += __shfl_down_sync(0xffffffffu, cF, o);
         }
         if (lane == 0) {
             atomicAdd(P.counters + 0, (unsigned long long)cR);
             atomicAdd(P.counters + 1, (unsigned long long)cE);
             atomicAdd(P.counters + 2, (unsigned long long)cS);
+            if (cF) atomicAdd(P.counters + 3, (unsigned long long)cF);
         }
     }
 }

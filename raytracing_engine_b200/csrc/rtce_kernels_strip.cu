@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
     const int tasks = tiles * P.frames;
     const int nwarps = gridDim.x * (kStripThreads / 32);
     const unsigned lt = (1u << lane) - 1u;
-    unsigned cR = 0, cE = 0, cS = 0;
+    unsigned cR = 0, cE = 0, cS = 0, cF = 0;   // cF: rays resolved by the far-miss shortcut (a subset of cR)
     int qn = 0;   // warp-uniform
 
     // Tasks (frame-major) are handed out dynamically, one atomic per task fetched one task ahead:
@@ -375,7 +375,7 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
 #pragma unroll
                         for (int rr = 0; rr < 2 * kFarPairs; rr++)
                             if (rr < rows) o[(size_t)rr * P.w] = fadd(pv[rr >> 1], rd);   // :84, :86 (positive)
-                        if (COUNT) { cR += (unsigned)rows; cE += (unsigned)(N * rows); cS += (unsigned)rows; }
+                        if (COUNT) { cR += (unsigned)rows; cE += (unsigned)(N * rows); cS += (unsigned)rows; cF += (unsigned)rows; }
                     }
                     ndone++;
                     ticket = __shfl_sync(RTCE_FULL, next, 0);
@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
                 // every ray of the row starts beyond every sphere by more than RENDER_DIST: all distances[i] >=
                 // RENDER_DIST, so the first trip takes dist = RENDER_DIST, is no hit and ends the march (:44-66)
                 if (xok) *op = fadd(start, rd);   // :84, :86 (positive)
-                if (COUNT && xok) { cR++; cE += (unsigned)N; cS++; }
+                if (COUNT && xok) { cR++; cE += (unsigned)N; cS++; cF++; }
                 if ((yb + rr) & 1) {   // next row starts a new pair
                     start = ahead;
                     if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
@@ -462,11 +462,13 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
             cR += __shfl_down_sync(RTCE_FULL, cR, o);
             cE += __shfl_down_sync(RTCE_FULL, cE, o);
             cS += __shfl_down_sync(RTCE_FULL, cS, o);
+            cF += __shfl_down_sync(RTCE_FULL, cF, o);
         }
         if (lane == 0) {
             atomicAdd(P.counters + 0, (unsigned long long)cR);
             atomicAdd(P.counters + 1, (unsigned long long)cE);
             atomicAdd(P.counters + 2, (unsigned long long)cS);
+            if (cF) atomicAdd(P.counters + 3, (unsigned long long)cF);
         }
     }
 }

@@ -36,7 +36,7 @@ EXPORTS = [
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
     "rtce_trace_accumulate", "rtce_accum_info", "rtce_readback", "rtce_readback_accum",
     "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_flush", "rtce_get_counters",
-    "rtce_get_level_counters",
+    "rtce_get_level_counters", "rtce_get_far_miss_rays",
     "rtce_shade_batch", "rtce_color_info", "rtce_readback_color", "rtce_readback_color_rgba8", "rtce_get_shade_counters",
     "rtce_measure_fp32_issue", "rtce_selftest_math", "rtce_debug_strip_timeline",
     "rtce_debug_launch_timeline",
@@ -95,6 +95,7 @@ def load_library() -> C.CDLL:
         "rtce_flush": (i32, [vp]),
         "rtce_get_counters": (i32, [vp, C.POINTER(_Counters)]),
         "rtce_get_level_counters": (i32, [vp, i32, C.POINTER(_Counters)]),
+        "rtce_get_far_miss_rays": (i32, [vp, i32, C.POINTER(C.c_uint64)]),
         "rtce_shade_batch": (i32, [vp, vp, i32]),
         "rtce_color_info": (i32, [vp, i32, C.POINTER(i32), C.POINTER(i32), C.POINTER(vp)]),
         "rtce_readback_color": (i32, [vp, i32, vp]),
@@ -359,6 +360,12 @@ class Engine:
         c = _Counters()
         self._check(self.lib.rtce_get_level_counters(self._ctx, level, C.byref(c)), "rtce_get_level_counters")
         return {"R": int(c.rays), "E": int(c.sdf_evals), "S": int(c.march_steps)}
+
+    def far_miss_rays(self, level: int = -1) -> int:
+        """Rays of the last counted call resolved by the far-miss shortcut (level < 0: every level)."""
+        o = C.c_uint64()
+        self._check(self.lib.rtce_get_far_miss_rays(self._ctx, level, C.byref(o)), "rtce_get_far_miss_rays")
+        return int(o.value)
 
     def counters(self) -> dict:
         c = _Counters()
