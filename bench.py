@@ -253,7 +253,7 @@ def run_ours(args, wl):
     if not weak:
         frames_rank = frames
     pcs = rt.make_push_constants(rots, poss)
-    steps = args.steps if args.steps is not None else (1000 if frames_rank * wl["W"] * wl["H"] < 1e9 else 3)
+    steps = args.steps if args.steps is not None else (1000 if frames_rank * wl["W"] * wl["H"] < 1e9 and wl["scene"] == "default" else 3)
     warmup = args.warmup if args.warmup is not None else (20 if steps >= 50 else 3)
     warmup = max(warmup, 3)
 

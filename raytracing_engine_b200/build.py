@@ -12,7 +12,7 @@ import subprocess
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "librtce.so")
-SOURCES = ["rtce_api.cu", "rtce_kernels.cu", "rtce_kernels_large.cu", "rtce_kernels_fused.cu", "rtce_kernels_strip.cu", "rtce_kernels_coarse.cu", "rtce_kernels_shade.cu",
+SOURCES = ["rtce_api.cu", "rtce_kernels.cu", "rtce_kernels_large.cu", "rtce_kernels_large_reg.cu", "rtce_kernels_fused.cu", "rtce_kernels_strip.cu", "rtce_kernels_coarse.cu", "rtce_kernels_shade.cu",
            "rtce_measure.cu"]
 DEPS = ["rtce_api_trace.inc", "rtce_device.cuh", "rtce_march.cuh", "rtce_shade_math.cuh", "rtce_kernels.cuh", "rtce_host.hpp", "../../include/rtce.h"]
 

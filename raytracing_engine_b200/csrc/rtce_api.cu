@@ -58,6 +58,7 @@ struct rtce_ctx {
     int coarse_mode = 0;                 // RTCE_OPT_COARSE_FUSED: 0 one launch per level, 1 fused-pyramid kernel, 2 cluster kernel
     int strip_rows = 16;                 // RTCE_OPT_STRIP_ROWS
     int strip_ctas_per_sm = 0;           // RTCE_OPT_STRIP_CTAS_PER_SM (0 = every resident slot)
+    int large_mode = 0;                  // RTCE_OPT_LARGE_KERNEL: 0 auto, 1 shared-memory kernel, 2 register kernel
     bool far_cull = true;                // RTCE_OPT_FAR_MISS: resolve rays that start beyond every sphere without SDFs
     // diagnostics (rtce_debug_launch_timeline): an event pair around every kernel launch
     struct LaunchMark { cudaEvent_t e0, e1; int kind, level, group; };
@@ -360,6 +361,10 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             c->strip_rows = (int)value;
             return RTCE_OK;
         case RTCE_OPT_FAR_MISS: c->far_cull = value != 0; return RTCE_OK;
+        case RTCE_OPT_LARGE_KERNEL:
+            if (value < 0 || value > 2) return fail(c, RTCE_ERR_INVALID, "large-scene kernel out of range");
+            c->large_mode = (int)value;
+            return RTCE_OK;
         case RTCE_OPT_STRIP_CTAS_PER_SM:
             if (value < 0 || value > 8) return fail(c, RTCE_ERR_INVALID, "strip CTAs per SM out of range");
             c->strip_ctas_per_sm = (int)value;

@@ -60,6 +60,9 @@ struct LevelParamsLarge {
     Cam cam[kMaxBatch];
 };
 cudaError_t launch_trace_level_large(const LevelParamsLarge& p, int frames, bool count, cudaStream_t st);
+// Same contract, the per-ray cache of lower bounds in registers (rtce_kernels_large_reg.cu); n_spheres <= large_reg_capacity().
+cudaError_t launch_trace_level_large_reg(const LevelParamsLarge& p, int frames, bool count, cudaStream_t st);
+int large_reg_capacity();
 
 // ---- fused pyramid kernel (objCount <= 8): ALL levels of a frame batch in ONE launch ---------
 // One CTA owns one 64x64 tile of the final level and, before it, the tile's ancestor regions on

@@ -21,6 +21,7 @@ OPT_GRAPH = 8
 OPT_FRAMES_IN_FLIGHT = 9
 OPT_STRIP_CTAS_PER_SM = 10
 OPT_FAR_MISS = 11
+OPT_LARGE_KERNEL = 12
 KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED, KERNEL_STRIP = 0, 1, 2, 3
 
 # compute.glsl:7-12 PushConstantData, 40 bytes

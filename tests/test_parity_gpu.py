@@ -386,22 +386,40 @@ def test_shade_needs_materials_and_lights():
             e.shade(pcs)
 
 
-def test_large_scene_kernel_matches_checker():
-    """objCount > 8 (CTA-per-ray kernel) on a bigger synthetic scene than the golden cases."""
+@pytest.mark.parametrize("large_kernel,n", [(1, 3000), (2, 3000), (2, 300), (2, 9), (0, 5000), (1, 17000)])
+def test_large_scene_kernel_matches_checker(large_kernel, n):
+    """objCount > 8 on bigger synthetic scenes than the golden cases: shared-memory kernel (1), register kernel (2:
+    one, two and three groups of eight objects per thread), auto (0)."""
     o = oracle.best()
-    sph = scene.synthetic_spheres(3000, seed=0xB200)
+    sph = scene.synthetic_spheres(n, seed=0xB200)
     rot, pos = camera.rotation(0.2, -0.1), np.array([0.5, 0.0, 1.0], np.float32)
-    ref, cnt = o.trace(sph, [96, 56], scene.view_ratio(96, 56), rot, pos, 1000.0, 0)
+    view = [96, 56] if n <= 5000 else [40, 24]
+    ref, cnt = o.trace(sph, view, scene.view_ratio(*view), rot, pos, 1000.0, 0)
     with rt.Engine(0, 1000.0) as e:
         e.set_option(rt.OPT_COUNTERS, 1)
+        e.set_option(rt.OPT_LARGE_KERNEL, large_kernel)
         e.set_spheres(sph)
-        e.set_view(96, 56)
+        e.set_view(*view)
         e.trace(rt.make_push_constants([rot, rot], [pos, pos]))
         for slot in (0, 1):
             for i, b in enumerate(ref):
                 assert np.array_equal(_bits(e.readback(i, slot)), _bits(b)), (slot, i)
         c = e.counters()
         assert c["R"] == 2 * cnt["R"] and c["E"] == 2 * cnt["E"] and c["S"] == 2 * cnt["S"]
+        # the uncounted instantiation of the same kernel
+        e.set_option(rt.OPT_COUNTERS, 0)
+        e.trace(rt.make_push_constants([rot], [pos]))
+        assert np.array_equal(_bits(e.readback(len(ref) - 1, 0)), _bits(ref[-1]))
+
+
+def test_register_kernel_refuses_scenes_beyond_its_capacity():
+    sph = scene.synthetic_spheres(17000, seed=0xB200)
+    with rt.Engine(0, 1000.0) as e:
+        e.set_option(rt.OPT_LARGE_KERNEL, 2)
+        e.set_spheres(sph)
+        e.set_view(40, 24)
+        with pytest.raises(rt.RtceError):
+            e.trace(rt.make_push_constants([camera.IDENTITY_ROT], [[0, 0, 0]]))
 
 
 def test_error_paths():
