@@ -49,6 +49,7 @@ def parse_args():
                     help="RTCE_OPT_FRAMES_IN_FLIGHT for frame-by-frame workloads (default 6): batches of consecutive steps "
                          "rotate over this many windows of frame slots and overlap on the device; 1 = strict stream order")
     ap.add_argument("--strip-ctas", type=int, default=None, help="RTCE_OPT_STRIP_CTAS_PER_SM")
+    ap.add_argument("--large-kernel", type=int, default=None, help="RTCE_OPT_LARGE_KERNEL (objCount > 8): 0 auto, 1 shared-memory kernel, 2 register kernel")
     ap.add_argument("--graph", type=int, default=None, help="RTCE_OPT_GRAPH: 1 = replay the launch chain from a CUDA graph (default), 0 = issue every launch")
     ap.add_argument("--frames", type=int, default=None, help="override frames per step (labelled in config)")
     ap.add_argument("--levels", type=int, default=None, help="override pyramid levels (configs[3] sweep)")
@@ -56,6 +57,9 @@ def parse_args():
     ap.add_argument("--strip-min-rays", type=int, default=None, help="kernel plan 3: strip-kernel threshold (rays per launch)")
     ap.add_argument("--groups", type=int, default=None, help="kernel plan 3: frame groups per batch (1..8)")
     ap.add_argument("--strip-rows", type=int, default=None, help="kernel plan 3: rows per strip task")
+    ap.add_argument("--band-weight", type=float, default=None,
+                    help="N > 1, accumulating workloads: cost of a marched texel in background texels for the row-band cut "
+                         "(1 = equal bands; default: picked at set-up from timed steps)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--profile", action="store_true", help="short run for ncu: no e2e, no CPU baseline, no clock hold")
@@ -271,6 +275,8 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_GRAPH, args.graph)
     if args.strip_ctas is not None:
         eng.set_option(rt.OPT_STRIP_CTAS_PER_SM, args.strip_ctas)
+    if args.large_kernel is not None:
+        eng.set_option(rt.OPT_LARGE_KERNEL, args.large_kernel)
     in_flight = (args.in_flight or 1) if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 6)
     eng.set_option(rt.OPT_FRAMES_IN_FLIGHT, in_flight)
     slots = min(frames_rank, 16)
@@ -282,14 +288,51 @@ def run_ours(args, wl):
     eng.set_view(wl["W"], wl["H"], levels=wl["levels"])
     levels = eng.levels
     Wf, Hf, _ = eng.level_info(-1, 0)
-    y0, y1 = sharding.band_rows(Hf, world, rank)
-    if world > 1 and not weak:
-        eng.set_rect(0, y0, Wf, y1)
-
     def dev_final(nslots):
         _, _, p0 = eng.level_info(-1, 0)
         stride = (eng.level_info(-1, 1)[2] - p0) if nslots > 1 else Wf * Hf * 4
         return torch.as_tensor(_DevView(p0, (nslots, Hf, Wf), (stride, Wf * 4, 4)), device=f"cuda:{local_rank}")
+
+    # Row bands (accumulating workloads at N > 1).  Equal bands are badly balanced: the spheres sit in the middle
+    # rows and a background texel costs a fraction of a marched one (far-miss shortcut), so the bands are cut to
+    # equal ESTIMATED cost from one pilot frame (every rank traces the same pose, hence computes the same cuts
+    # without communication), and the one free parameter of the estimate (cost of a marched texel in background
+    # texels) is picked at set-up from a few timed steps, max over ranks.  Not in the timed region.
+    bands = sharding.all_bands(Hf, world)
+    band_info = None
+    y0, y1 = bands[rank]
+    if world > 1 and not weak:
+        with torch.cuda.stream(stream):
+            eng.trace(pcs[:1])
+            eng.sync()
+            pilot = dev_final(1)[0].clone()
+            cands = [args.band_weight] if args.band_weight is not None else [1.0, 4.0, 8.0, 16.0, 32.0]
+            trials = []
+            for hw in cands:
+                cb = sharding.all_bands(Hf, world) if hw == 1.0 else \
+                    sharding.weighted_bands(sharding.row_cost(pilot, scene.RENDER_DIST, hw), world)
+                ms = None
+                if len(cands) > 1:
+                    eng.set_rect(0, cb[rank][0], Wf, cb[rank][1])
+                    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    for k in range(2):   # the first pass captures the launch graphs of the new rect
+                        dist.barrier()
+                        torch.cuda.synchronize()
+                        ev0.record(stream)
+                        eng.trace_accumulate(pcs)
+                        ev1.record(stream)
+                        torch.cuda.synchronize()
+                    t = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=f"cuda:{local_rank}")
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                    ms = float(t.item())
+                trials.append((hw, ms, cb))
+            hw, ms, bands = min(trials, key=lambda t: (t[1] is None, t[1] or 0.0)) if len(trials) > 1 else trials[0]
+            y0, y1 = bands[rank]
+            eng.set_rect(0, y0, Wf, y1)
+            band_info = {"rows_per_rank": [b1 - b0 for b0, b1 in bands], "marched_texel_weight": hw,
+                         "set_up_trials_ms_per_step": {str(t[0]): t[1] for t in trials},
+                         "note": "contiguous bands of equal estimated cost (row cost from one pilot frame: width + (weight - 1) x marched texels), "
+                                 "weight picked at set-up by timing one step per candidate (max over ranks); weight 1 = equal bands"}
 
     def step():
         """One pass of the hot path over the batch, inputs resident; N>1: + the one gather to rank 0."""
@@ -300,7 +343,7 @@ def run_ours(args, wl):
                 pw, ph, pp = C.c_int(), C.c_int(), C.c_void_p()
                 eng._check(eng.lib.rtce_accum_info(eng._ctx, C.byref(pw), C.byref(ph), C.byref(pp)), "rtce_accum_info")
                 acc = torch.as_tensor(_DevView(pp.value, (1, Hf, Wf), (Wf * Hf * 4, Wf * 4, 4)), device=f"cuda:{local_rank}")
-                return sharding.gather_bands(acc[:, y0:y1, :], Hf, dst=0)
+                return sharding.gather_bands(acc[:, y0:y1, :], Hf, dst=0, bands=bands)
         else:
             eng.trace(pcs)
         return None
@@ -549,9 +592,11 @@ def run_ours(args, wl):
                                    "fixed work per GPU), whole image per frame, results stay in each rank's HBM; no data-path "
                                    "collective (frames are independent units)" if weak else
                                    f"{n_gpus} row bands of the final level + one NCCL gather of the accumulated image to rank 0 per step"),
+                   "bands": band_info,
                    "frames_in_flight": in_flight if not wl["accumulate"] else f"{max(in_flight, 4)} chunks (internal to rtce_trace_accumulate)",
                    "l2": f"no flush: each step rewrites {bytes_step / 1e6:.0f} MB of pyramid (> 126 MB L2 when frames >= 12 at 1080p); parents are meant to be L2 hits",
-                   "kernel": {0: "auto (strip kernel + overflow launch per fine level, one per-pixel launch per coarse level)", 1: "per-level", 2: "fused", 3: "strip kernel + overflow launch per fine level, one per-pixel launch per coarse level"}[args.kernel]},
+                   "kernel": {0: "auto (strip kernel + overflow launch per fine level, one per-pixel launch per coarse level)", 1: "per-level", 2: "fused", 3: "strip kernel + overflow launch per fine level, one per-pixel launch per coarse level"}[args.kernel]
+                   if len(spheres) <= 8 else {None: "large-scene kernel, auto (register kernel: per-ray bounds in registers, one CTA per ray)", 0: "large-scene kernel, auto (register kernel)", 1: "large-scene kernel, shared-memory version", 2: "large-scene kernel, register version"}[args.large_kernel]},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches_per_step * steps) * n_gpus,
         "roofline": roofline, "cpu_baseline": cpu_baseline,
         "mprimary_per_s": Wf * Hf * frames / (ms_step * 1e-3) / 1e6,

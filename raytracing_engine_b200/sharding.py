@@ -27,20 +27,77 @@ def all_bands(height: int, world: int, align: int = BAND_ALIGN):
     return [band_rows(height, world, r, align) for r in range(world)]
 
 
-def gather_bands(local: torch.Tensor, height: int, dst: int = 0, group=None):
+def weighted_bands(row_weights, world: int, align: int = BAND_ALIGN):
+    """Contiguous row bands of (nearly) equal total weight: [(y0, y1)] * world, boundaries on multiples of `align`,
+    every band at least `align` rows.  `row_weights[y]` is the estimated cost of final-level row y (e.g.
+    `row_cost` below).  Pure function of its arguments, so every rank computes the same partition from the same
+    pilot frame without talking to the others.  Equal weights reproduce `all_bands` up to rounding."""
+    import numpy as np
+    w = np.asarray(row_weights, dtype=np.float64).reshape(-1)
+    height = int(w.shape[0])
+    units = (height + align - 1) // align
+    if units < world:
+        raise ValueError(f"{height} rows cannot be split into {world} bands of {align}-row units")
+    pad = np.zeros(units * align, dtype=np.float64)
+    pad[:height] = np.maximum(w, 0.0)
+    uw = pad.reshape(units, align).sum(axis=1) + 1e-12   # strictly increasing prefix sums
+    cum = np.concatenate([[0.0], np.cumsum(uw)])
+    cuts = [0]
+    for k in range(1, world):
+        target = cum[-1] * k / world
+        u = int(np.searchsorted(cum, target))            # first prefix >= target
+        if u > 0 and target - cum[u - 1] < cum[u] - target:
+            u -= 1                                       # nearer boundary
+        u = max(u, cuts[-1] + 1)                         # at least one unit per band ...
+        u = min(u, units - (world - k))                  # ... for the bands still to come, too
+        cuts.append(u)
+    cuts.append(units)
+    return [(min(a * align, height), min(b * align, height)) for a, b in zip(cuts, cuts[1:])]
+
+
+def row_cost(final_level: torch.Tensor, render_dist: float, hit_weight: float):
+    """Estimated cost of each final-level row from one traced frame [rows, width]: a texel that reached
+    RENDER_DIST is background (resolved by the far-miss shortcut: a load, a compare and a store), anything else
+    is marched (second trips, tails); `hit_weight` = cost of a marched texel in units of a background texel."""
+    marched = (final_level < render_dist).sum(dim=-1).to(torch.float64)
+    return (final_level.shape[-1] + (hit_weight - 1.0) * marched).cpu().numpy()
+
+
+def gather_bands(local: torch.Tensor, height: int, dst: int = 0, group=None, bands=None):
     """Gather per-rank bands `local` = [..., rows_r, width] into [..., height, width] on rank `dst`.
 
-    One collective: every rank contributes a band padded to the largest band height
-    (dist.gather needs equal shapes); rank `dst` strips the padding.  Returns the full image on
-    `dst`, None elsewhere.
+    `bands` = [(y0, y1)] per rank (default: the equal split `all_bands`).  One exchange step: a row band of a
+    row-major image is contiguous, so when there is a single leading image every rank sends exactly its rows and
+    rank `dst` receives them in place (batched point-to-point, no padding, no copy).  With several leading images the
+    bands are padded to the largest band height and gathered with one dist.gather.  Returns the full image on `dst`,
+    None elsewhere.
     """
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
-    bands = all_bands(height, world)
-    max_rows = max(y1 - y0 for (y0, y1) in bands)
+    if bands is None:
+        bands = all_bands(height, world)
+    assert len(bands) == world and bands[0][0] == 0 and bands[-1][1] == height, bands
     y0, y1 = bands[rank]
     assert local.shape[-2] == y1 - y0, (local.shape, bands[rank])
     lead, width = local.shape[:-2], local.shape[-1]
+    n_lead = 1
+    for d in lead:
+        n_lead *= int(d)
+    if n_lead == 1:
+        if rank == dst:
+            full = local.new_empty(*lead, height, width)
+            flat = full.view(height, width)
+            flat[y0:y1] = local.reshape(y1 - y0, width)
+            ops = [dist.P2POp(dist.irecv, flat[b0:b1], r, group) for r, (b0, b1) in enumerate(bands) if r != dst and b1 > b0]
+            if ops:
+                for req in dist.batch_isend_irecv(ops):
+                    req.wait()
+            return full
+        if y1 > y0:
+            for req in dist.batch_isend_irecv([dist.P2POp(dist.isend, local.reshape(y1 - y0, width).contiguous(), dst, group)]):
+                req.wait()
+        return None
+    max_rows = max(b1 - b0 for (b0, b1) in bands)
     if y1 - y0 == max_rows:
         send = local.contiguous()
     else:

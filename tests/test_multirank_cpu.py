@@ -83,3 +83,68 @@ def test_banded_trace_plus_gather_is_bit_identical(world, W, H):
         p.join(120)
         assert p.exitcode == 0
     assert q.get(timeout=5) is True
+
+
+def test_weighted_bands_balance_cost_in_multiples_of_8():
+    rs = np.random.RandomState(7)
+    for H in (136, 600, 1080, 4320):
+        for world in (2, 3, 8):
+            w = np.ones(H)
+            a = int(rs.randint(0, H // 2))
+            w[a:a + H // 4] += rs.uniform(2, 30)
+            bands = sharding.weighted_bands(w, world)
+            assert len(bands) == world and bands[0][0] == 0 and bands[-1][1] == H
+            for (a0, a1), (b0, b1) in zip(bands, bands[1:]):
+                assert a1 == b0
+            for (y0, y1) in bands:
+                assert y1 > y0 and y0 % 8 == 0 and (y1 % 8 == 0 or y1 == H)
+            cost = [w[y0:y1].sum() for y0, y1 in bands]
+            # no band is heavier than the ideal share by more than one 8-row unit of the heaviest rows
+            assert max(cost) <= w.sum() / world + 8 * w.max() + 1e-9
+    assert sharding.weighted_bands(np.ones(4320), 8)[3] == (1616, 2160)
+    with pytest.raises(ValueError):
+        sharding.weighted_bands(np.ones(16), 3)
+
+
+def _worker_weighted(rank, world, port, W, H, q):
+    """Cost-balanced bands cut from a pilot frame + the in-place point-to-point gather of ONE accumulated image."""
+    sys.path.insert(0, ROOT)
+    import oracle
+    from raytracing_engine_b200 import camera, scene
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        o = oracle.load("port")
+        sph = scene.spheres_of(scene.default_mutable_data())
+        n = o.level_count(float(W))
+        Wf, Hf = o.level_dims(n, float(W), float(H))[-1]
+        rots, poss = camera.static_path(1)
+        args = (sph, [W, H], scene.view_ratio(W, H), rots[0], poss[0], 1000.0, n)
+        pilot, _ = o.trace(*args, threads=1)
+        bands = sharding.weighted_bands(sharding.row_cost(torch.from_numpy(pilot[-1]), 1000.0, 8.0), world)
+        y0, y1 = bands[rank]
+        lv, _ = o.trace(*args, rect=[0, y0, Wf, y1], threads=1)
+        local = torch.from_numpy(lv[-1][y0:y1].copy())[None]
+        full = sharding.gather_bands(local, Hf, dst=0, bands=bands)
+        if rank == 0:
+            sizes = [b1 - b0 for b0, b1 in bands]
+            q.put(bool(np.array_equal(full[0].numpy().view(np.uint32), pilot[-1].view(np.uint32))) and max(sizes) > min(sizes))
+        else:
+            assert full is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_weighted_bands_plus_in_place_gather_is_bit_identical(world):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_weighted, args=(r, world, port, 320, 200, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True

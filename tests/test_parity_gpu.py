@@ -391,6 +391,8 @@ def test_large_scene_kernel_matches_checker(large_kernel, n):
     """objCount > 8 on bigger synthetic scenes than the golden cases: shared-memory kernel (1), register kernel (2:
     one, two and three groups of eight objects per thread), auto (0)."""
     o = oracle.best()
+    if n > o.max_objects:   # beyond the raised MAX_OBJECTS of oracle/_ref's second build: the C restatement has no limit
+        o = oracle.load("port")
     sph = scene.synthetic_spheres(n, seed=0xB200)
     rot, pos = camera.rotation(0.2, -0.1), np.array([0.5, 0.0, 1.0], np.float32)
     view = [96, 56] if n <= 5000 else [40, 24]
