@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--strip-min-rays", type=int, default=None, help="kernel plan 3: strip-kernel threshold (rays per launch)")
     ap.add_argument("--groups", type=int, default=None, help="kernel plan 3: frame groups per batch (1..8)")
     ap.add_argument("--strip-rows", type=int, default=None, help="kernel plan 3: rows per strip task")
+    ap.add_argument("--slots", type=int, default=None, help="RTCE_OPT_FRAME_SLOTS: frames per chunk / launch (default min(frames, 16), at most 32)")
     ap.add_argument("--band-weight", type=float, default=None,
                     help="N > 1, accumulating workloads: cost of a marched texel in background texels for the row-band cut "
                          "(1 = equal bands; default: picked at set-up from timed steps)")
@@ -257,7 +258,7 @@ def run_ours(args, wl):
     if not weak:
         frames_rank = frames
     pcs = rt.make_push_constants(rots, poss)
-    steps = args.steps if args.steps is not None else (1000 if frames_rank * wl["W"] * wl["H"] < 1e9 and wl["scene"] == "default" else 3)
+    steps = args.steps if args.steps is not None else (1000 if frames_rank * wl["W"] * wl["H"] < 1e9 and wl["scene"] == "default" else (3 if world == 1 or weak else 10))
     warmup = args.warmup if args.warmup is not None else (20 if steps >= 50 else 3)
     warmup = max(warmup, 3)
 
@@ -277,9 +278,13 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_STRIP_CTAS_PER_SM, args.strip_ctas)
     if args.large_kernel is not None:
         eng.set_option(rt.OPT_LARGE_KERNEL, args.large_kernel)
-    in_flight = (args.in_flight or 1) if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 6)
+    # accumulating workloads: rtce_trace_accumulate rotates its chunks over max(in_flight, 4) lanes internally; with row
+    # bands (N > 1) a launch carries 1/N of the rays, so more chunks in flight and larger chunks keep the machine busy
+    # (measured at N = 8: 4 lanes x 16 frames 37.9 ms, 8 lanes x 32 frames 33.4 ms per step)
+    band_mode = world > 1 and wl["accumulate"]
+    in_flight = (args.in_flight or (8 if band_mode else 1)) if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 6)
     eng.set_option(rt.OPT_FRAMES_IN_FLIGHT, in_flight)
-    slots = min(frames_rank, 16)
+    slots = min(frames_rank, args.slots or (32 if band_mode else 16), 32)
     eng.set_option(rt.OPT_FRAME_SLOTS, slots)
     if len(spheres) <= 8:
         eng.set_scene(scene.pack_mutable_data(objects=[(tuple(s[:3]), s[3]) for s in spheres]))
@@ -306,7 +311,7 @@ def run_ours(args, wl):
             eng.trace(pcs[:1])
             eng.sync()
             pilot = dev_final(1)[0].clone()
-            cands = [args.band_weight] if args.band_weight is not None else [1.0, 4.0, 8.0, 16.0, 32.0]
+            cands = [args.band_weight] if args.band_weight is not None else [1.0, 2.0, 4.0]
             trials = []
             for hw in cands:
                 cb = sharding.all_bands(Hf, world) if hw == 1.0 else \
@@ -334,6 +339,13 @@ def run_ours(args, wl):
                          "note": "contiguous bands of equal estimated cost (row cost from one pilot frame: width + (weight - 1) x marched texels), "
                                  "weight picked at set-up by timing one step per candidate (max over ranks); weight 1 = equal bands"}
 
+    gather_state = {}
+
+    def finish_gathers():
+        """Order the launching stream after every gather still in flight (before the end event of a timed region)."""
+        for ev in gather_state.get("done", []):
+            stream.wait_event(ev)
+
     def step():
         """One pass of the hot path over the batch, inputs resident; N>1: + the one gather to rank 0."""
         if wl["accumulate"]:
@@ -343,7 +355,26 @@ def run_ours(args, wl):
                 pw, ph, pp = C.c_int(), C.c_int(), C.c_void_p()
                 eng._check(eng.lib.rtce_accum_info(eng._ctx, C.byref(pw), C.byref(ph), C.byref(pp)), "rtce_accum_info")
                 acc = torch.as_tensor(_DevView(pp.value, (1, Hf, Wf), (Wf * Hf * 4, Wf * 4, 4)), device=f"cuda:{local_rank}")
-                return sharding.gather_bands(acc[:, y0:y1, :], Hf, dst=0, bands=bands)
+                # The gather of step k overlaps the tracing of step k + 1: the band is copied out of the accumulator
+                # (which the next step overwrites) into one of two buffers and gathered from there on a side stream.
+                G = gather_state
+                if not G:
+                    G["side"] = torch.cuda.Stream(device=local_rank)
+                    G["band"] = [torch.empty((1, y1 - y0, Wf), dtype=torch.float32, device=f"cuda:{local_rank}") for _ in range(2)]
+                    G["full"] = [torch.empty((1, Hf, Wf), dtype=torch.float32, device=f"cuda:{local_rank}") if rank == 0 else None for _ in range(2)]
+                    G["ready"] = [torch.cuda.Event() for _ in range(2)]
+                    G["done"] = [torch.cuda.Event() for _ in range(2)]
+                    G["k"] = 0
+                k = G["k"] % 2
+                G["k"] += 1
+                stream.wait_event(G["done"][k])          # the gather that last read buffer k has finished
+                G["band"][k].copy_(acc[:, y0:y1, :])
+                G["ready"][k].record(stream)
+                with torch.cuda.stream(G["side"]):
+                    G["side"].wait_event(G["ready"][k])
+                    full = sharding.gather_bands(G["band"][k], Hf, dst=0, bands=bands, out=G["full"][k])
+                    G["done"][k].record(G["side"])
+                return full
         else:
             eng.trace(pcs)
         return None
@@ -394,6 +425,7 @@ def run_ours(args, wl):
         for _ in range(steps):
             step()
         eng.flush()   # frames in flight: the end event comes after every batch
+        finish_gathers()   # ... and after every gather
         e1.record(stream)
         barrier()
         ms_total = e0.elapsed_time(e1)
@@ -509,6 +541,26 @@ def run_ours(args, wl):
                        "copied to pinned host memory (accumulate workloads: the one accumulated image); N>1: each rank "
                        "returns its own frames (accumulate workloads: its row band) to its host buffer"}
 
+    # ---- N > 1, row bands: the gathered image on rank 0 against the same job traced whole on rank 0 (not timed) ----
+    gather_check = None
+    if world > 1 and not weak:
+        import ctypes as C
+        with torch.cuda.stream(stream):
+            full = step()
+            finish_gathers()
+            barrier()
+            if rank == 0:
+                got = full.clone()
+                eng.set_rect(0, 0, Wf, Hf)
+                eng.trace_accumulate(pcs)
+                eng.sync()
+                pw, ph, pp = C.c_int(), C.c_int(), C.c_void_p()
+                eng._check(eng.lib.rtce_accum_info(eng._ctx, C.byref(pw), C.byref(ph), C.byref(pp)), "rtce_accum_info")
+                whole = torch.as_tensor(_DevView(pp.value, (1, Hf, Wf), (Wf * Hf * 4, Wf * 4, 4)), device=f"cuda:{local_rank}")
+                same = bool(torch.equal(got.view(torch.int32), whole.view(torch.int32)))
+                torch.cuda.synchronize()
+                gather_check = "bit-identical to the whole image traced on rank 0" if same else "MISMATCH"
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -592,8 +644,8 @@ def run_ours(args, wl):
                                    "fixed work per GPU), whole image per frame, results stay in each rank's HBM; no data-path "
                                    "collective (frames are independent units)" if weak else
                                    f"{n_gpus} row bands of the final level + one NCCL gather of the accumulated image to rank 0 per step"),
-                   "bands": band_info,
-                   "frames_in_flight": in_flight if not wl["accumulate"] else f"{max(in_flight, 4)} chunks (internal to rtce_trace_accumulate)",
+                   "bands": band_info, "gather_check": gather_check,
+                   "frames_in_flight": in_flight if not wl["accumulate"] else f"{max(in_flight, 4)} chunks of {slots} frames (internal to rtce_trace_accumulate)",
                    "l2": f"no flush: each step rewrites {bytes_step / 1e6:.0f} MB of pyramid (> 126 MB L2 when frames >= 12 at 1080p); parents are meant to be L2 hits",
                    "kernel": {0: "auto (strip kernel + overflow launch per fine level, one per-pixel launch per coarse level)", 1: "per-level", 2: "fused", 3: "strip kernel + overflow launch per fine level, one per-pixel launch per coarse level"}[args.kernel]
                    if len(spheres) <= 8 else {None: "large-scene kernel, auto (register kernel: per-ray bounds in registers, one CTA per ray)", 0: "large-scene kernel, auto (register kernel)", 1: "large-scene kernel, shared-memory version", 2: "large-scene kernel, register version"}[args.large_kernel]},

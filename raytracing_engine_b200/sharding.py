@@ -63,14 +63,14 @@ def row_cost(final_level: torch.Tensor, render_dist: float, hit_weight: float):
     return (final_level.shape[-1] + (hit_weight - 1.0) * marched).cpu().numpy()
 
 
-def gather_bands(local: torch.Tensor, height: int, dst: int = 0, group=None, bands=None):
+def gather_bands(local: torch.Tensor, height: int, dst: int = 0, group=None, bands=None, out=None):
     """Gather per-rank bands `local` = [..., rows_r, width] into [..., height, width] on rank `dst`.
 
     `bands` = [(y0, y1)] per rank (default: the equal split `all_bands`).  One exchange step: a row band of a
     row-major image is contiguous, so when there is a single leading image every rank sends exactly its rows and
     rank `dst` receives them in place (batched point-to-point, no padding, no copy).  With several leading images the
-    bands are padded to the largest band height and gathered with one dist.gather.  Returns the full image on `dst`,
-    None elsewhere.
+    bands are padded to the largest band height and gathered with one dist.gather.  `out` (rank `dst`, single image):
+    a preallocated [..., height, width] tensor to receive into.  Returns the full image on `dst`, None elsewhere.
     """
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
@@ -85,7 +85,7 @@ def gather_bands(local: torch.Tensor, height: int, dst: int = 0, group=None, ban
         n_lead *= int(d)
     if n_lead == 1:
         if rank == dst:
-            full = local.new_empty(*lead, height, width)
+            full = out if out is not None else local.new_empty(*lead, height, width)
             flat = full.view(height, width)
             flat[y0:y1] = local.reshape(y1 - y0, width)
             ops = [dist.P2POp(dist.irecv, flat[b0:b1], r, group) for r, (b0, b1) in enumerate(bands) if r != dst and b1 > b0]
