@@ -115,8 +115,8 @@ typedef enum rtce_option {
                                    RENDER_DIST (host-side conservative bound per camera) is resolved as start + RENDER_DIST
                                    without evaluating an SDF: exactly what compute.glsl:37-66 computes for it (all
                                    distances[i] >= RENDER_DIST -> one trip, no hit).  0 = evaluate every ray in full. */
-    RTCE_OPT_LARGE_KERNEL = 12, /* objCount > 8 (extension of utilities.glsl:3): 0 (default) = auto: the register kernel when the
-                                   scene fits it (<= 16384 spheres), else the shared-memory kernel; 1 = shared-memory kernel (per-ray
+    RTCE_OPT_LARGE_KERNEL = 12, /* objCount > 8 (extension of utilities.glsl:3): 0 (default) = auto: the register kernel
+                                   (its capacity, 16384 spheres, is RTCE_MAX_SPHERES); 1 = shared-memory kernel (per-ray
                                    cache of lower bounds as float4 groups in shared memory, any count that fits 200 KB);
                                    2 = register kernel (the cache as an unrolled register array, 8 x G8 objects per thread). */
     RTCE_OPT_GRAPH = 8,         /* kernel plan 3: 1 (default) = the launch chain of a frame batch (every level of every group,

@@ -386,10 +386,10 @@ def test_shade_needs_materials_and_lights():
             e.shade(pcs)
 
 
-@pytest.mark.parametrize("large_kernel,n", [(1, 3000), (2, 3000), (2, 300), (2, 9), (0, 5000), (1, 17000)])
+@pytest.mark.parametrize("large_kernel,n", [(1, 3000), (2, 3000), (2, 300), (2, 9), (0, 5000), (2, 7000), (2, 10000), (2, 12000), (0, 16384), (1, 16384)])
 def test_large_scene_kernel_matches_checker(large_kernel, n):
     """objCount > 8 on bigger synthetic scenes than the golden cases: shared-memory kernel (1), register kernel (2:
-    one, two and three groups of eight objects per thread), auto (0)."""
+    every instantiation, 1 to 8 groups of eight objects per thread, up to RTCE_MAX_SPHERES), auto (0)."""
     o = oracle.best()
     if n > o.max_objects:   # beyond the raised MAX_OBJECTS of oracle/_ref's second build: the C restatement has no limit
         o = oracle.load("port")
@@ -414,14 +414,12 @@ def test_large_scene_kernel_matches_checker(large_kernel, n):
         assert np.array_equal(_bits(e.readback(len(ref) - 1, 0)), _bits(ref[-1]))
 
 
-def test_register_kernel_refuses_scenes_beyond_its_capacity():
-    sph = scene.synthetic_spheres(17000, seed=0xB200)
+def test_set_spheres_refuses_more_than_the_limit():
+    """RTCE_MAX_SPHERES (16384) is also the capacity of the register kernel: every accepted scene has a kernel."""
+    sph = scene.synthetic_spheres(16385, seed=0xB200)
     with rt.Engine(0, 1000.0) as e:
-        e.set_option(rt.OPT_LARGE_KERNEL, 2)
-        e.set_spheres(sph)
-        e.set_view(40, 24)
         with pytest.raises(rt.RtceError):
-            e.trace(rt.make_push_constants([camera.IDENTITY_ROT], [[0, 0, 0]]))
+            e.set_spheres(sph)
 
 
 def test_error_paths():
