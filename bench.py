@@ -278,13 +278,13 @@ def run_ours(args, wl):
         eng.set_option(rt.OPT_STRIP_CTAS_PER_SM, args.strip_ctas)
     if args.large_kernel is not None:
         eng.set_option(rt.OPT_LARGE_KERNEL, args.large_kernel)
-    # accumulating workloads: rtce_trace_accumulate rotates its chunks over max(in_flight, 4) lanes internally; with row
-    # bands (N > 1) a launch carries 1/N of the rays, so more chunks in flight and larger chunks keep the machine busy
-    # (measured at N = 8: 4 lanes x 16 frames 37.9 ms, 8 lanes x 32 frames 33.4 ms per step)
+    # accumulating workloads: rtce_trace_accumulate rotates its chunks over max(in_flight, 4) lanes internally; 8 lanes x
+    # 32-frame chunks keep the machine busier than 4 x 16 (c4, N = 1: 220.9 -> 210.1 ms per step; with row bands a launch
+    # carries 1/N of the rays and it matters more: N = 8, 37.9 -> 33.4 ms)
     band_mode = world > 1 and wl["accumulate"]
-    in_flight = (args.in_flight or (8 if band_mode else 1)) if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 6)
+    in_flight = (args.in_flight or 8) if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 6)
     eng.set_option(rt.OPT_FRAMES_IN_FLIGHT, in_flight)
-    slots = min(frames_rank, args.slots or (32 if band_mode else 16), 32)
+    slots = min(frames_rank, args.slots or (32 if wl["accumulate"] else 16), 32)
     eng.set_option(rt.OPT_FRAME_SLOTS, slots)
     if len(spheres) <= 8:
         eng.set_scene(scene.pack_mutable_data(objects=[(tuple(s[:3]), s[3]) for s in spheres]))
