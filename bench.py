@@ -105,7 +105,9 @@ class ClockSampler:
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
                0x80: "hw_power_brake_slowdown"}
 
-    def __init__(self, index):
+    def __init__(self, index, period=0.05):
+        # NVML queries take a driver lock that CUDA launches also want: 20 Hz, and only on rank 0 (bench_ours)
+        self.period = period
         self.samples, self.reasons, self.max_mhz, self.ok = [], set(), None, False
         self._stop = threading.Event()
         try:
@@ -129,7 +131,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.01)
+            self._stop.wait(self.period)
 
     def start(self):
         if self.ok:
@@ -137,7 +139,7 @@ class ClockSampler:
 
     def stop(self):
         self._stop.set()
-        if self.ok:
+        if self.ok and self.t.is_alive():
             self.t.join(1.0)
         med = int(np.median(self.samples)) if self.samples else None
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
@@ -419,7 +421,8 @@ def run_ours(args, wl):
         launches0 = 0
         sampler = ClockSampler(local_rank if "CUDA_VISIBLE_DEVICES" not in os.environ else
                                int(os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local_rank]))
-        sampler.start()
+        if rank == 0:
+            sampler.start()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         for _ in range(steps):
