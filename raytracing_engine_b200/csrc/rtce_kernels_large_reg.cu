@@ -84,16 +84,16 @@ __global__ void __launch_bounds__(kRegThreads, (G8 <= 5 ? 3 : 2))
         while (len < P.render_dist) {   // :44
             const float radius = fmul(fadd(len, 1.0f), P.threshold);
             float m = P.render_dist;   // :49
+            const float px = fadd(ox, fmul(dir.x, len));   // :46, once per trip (most trips enter several groups)
+            const float py = fadd(oy, fmul(dir.y, len));
+            const float pz = fadd(oz, fmul(dir.z, len));
 #pragma unroll
             for (int g = 0; g < G8; g++) {   // :51-57
                 float* v = d + 8 * g;
 #pragma unroll
                 for (int c = 0; c < 8; c++) v[c] = fsub(v[c], last);
                 float m8 = min8(v);
-                if (m8 <= radius) {   // rare: some bound of the group fell inside the cone radius
-                    const float px = fadd(ox, fmul(dir.x, len));
-                    const float py = fadd(oy, fmul(dir.y, len));
-                    const float pz = fadd(oz, fmul(dir.z, len));
+                if (m8 <= radius) {   // some bound of the group fell inside the cone radius
 #pragma unroll
                     for (int c = 0; c < 8; c++) {
                         if (v[c] <= radius) {
