@@ -40,6 +40,24 @@ RTCE_DEV V3 xyz(float4 v) { return {v.x, v.y, v.z}; }
 RTCE_DEV float sdf(V3 p, float4 s) { return fsub(v_length(v_sub(p, xyz(s))), s.w); }
 
 // fragment.glsl:89-121.
+// min / max inside shadow_ray: the specification's ternaries (lit_min / lit_max) differ from FMNMX only on a (+0, -0)
+// pair or a NaN.  Here a zero `dist` returns before its sign can matter (0 <= RAY_RADIUS), `last` and `nearest` are
+// only updated with dist > RAY_RADIUS > 0, and finite inputs produce no NaN: FMNMX yields the same bits in one
+// instruction instead of two.
+#ifndef RTCE_SHADE_FMNMX
+#define RTCE_SHADE_FMNMX 0
+#endif
+#if RTCE_SHADE_FMNMX
+#define SR_MIN(a, b) fminf(a, b)
+#define SR_MAX(a, b) fmaxf(a, b)
+#else
+#define SR_MIN(a, b) lit_min(a, b)
+#define SR_MAX(a, b) lit_max(a, b)
+#endif
+#ifndef RTCE_SHADE_CTAS
+#define RTCE_SHADE_CTAS 4
+#endif
+
 template <int N, bool COUNT>
 RTCE_DEV float shadow_ray(const ShadeParams& P, V3 origin, V3 step, float end, unsigned& cD) {
     const float RAY_RADIUS = 0.01f;
@@ -76,17 +94,17 @@ RTCE_DEV float shadow_ray(const ShadeParams& P, V3 origin, V3 step, float end, u
                 d[i] = refresh ? exact : bound;
             }
 #endif
-            dist = lit_min(dist, d[i]);
+            dist = SR_MIN(dist, d[i]);
         }
         if (dist <= RAY_RADIUS) return 0.0f;   // :113-115
-        last = lit_max(dist, 0.0f);
-        nearest = lit_min(nearest, dist);
+        last = SR_MAX(dist, 0.0f);
+        nearest = SR_MIN(nearest, dist);
     }
     return nearest;
 }
 
 template <int N, bool COUNT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, RTCE_SHADE_CTAS)
     k_shade(const __grid_constant__ ShadeParams P) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = P.x0 + blockIdx.x * 32 + (warp & 3) * 8 + (lane & 7);
