@@ -160,6 +160,13 @@ impl ConeMarcher {
         self.check(st)
     }
 
+    /// Kernel for scenes of more than 8 spheres (RTCE_OPT_LARGE_KERNEL = 12): 0 auto, 1 shared-memory version,
+    /// 2 register version.  No counterpart in the reference (utilities.glsl:3 caps MAX_OBJECTS at 8).
+    pub fn set_large_scene_kernel(&mut self, k: u32) -> Result<(), Error> {
+        let st = unsafe { rtce_set_option(self.ctx, 12, k as i64) };
+        self.check(st)
+    }
+
     /// Order the context's stream after every batch traced so far (no host wait).
     pub fn flush(&mut self) -> Result<(), Error> {
         let st = unsafe { rtce_flush(self.ctx) };
