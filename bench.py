@@ -283,7 +283,6 @@ def run_ours(args, wl):
     # accumulating workloads: rtce_trace_accumulate rotates its chunks over max(in_flight, 4) lanes internally; 8 lanes x
     # 32-frame chunks keep the machine busier than 4 x 16 (c4, N = 1: 220.9 -> 210.1 ms per step; with row bands a launch
     # carries 1/N of the rays and it matters more: N = 8, 37.9 -> 33.4 ms)
-    band_mode = world > 1 and wl["accumulate"]
     in_flight = (args.in_flight or 8) if wl["accumulate"] else (args.in_flight if args.in_flight is not None else 6)
     eng.set_option(rt.OPT_FRAMES_IN_FLIGHT, in_flight)
     slots = min(frames_rank, args.slots or (32 if wl["accumulate"] else 16), 32)
