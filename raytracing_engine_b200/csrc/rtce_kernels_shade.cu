@@ -45,7 +45,7 @@ RTCE_DEV float sdf(V3 p, float4 s) { return fsub(v_length(v_sub(p, xyz(s))), s.w
 // only updated with dist > RAY_RADIUS > 0, and finite inputs produce no NaN: FMNMX yields the same bits in one
 // instruction instead of two.
 #ifndef RTCE_SHADE_FMNMX
-#define RTCE_SHADE_FMNMX 0
+#define RTCE_SHADE_FMNMX 1
 #endif
 #if RTCE_SHADE_FMNMX
 #define SR_MIN(a, b) fminf(a, b)
