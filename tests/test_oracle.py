@@ -100,3 +100,25 @@ def test_hit_pixels_end_on_a_surface(case_table):
     rad = (f[ys, xs] + 1.0) * thr
     assert np.all(sdf <= 2.5 * rad + 1e-3)
     assert np.all(sdf >= -1e-3)
+
+
+def test_rays_only_advance_from_parent_to_child(case_table):
+    """SURVEY.md §4 v: a child starts where its parent stopped and `last = max(dist, 0)` (compute.glsl:59) never steps
+    back, so a child texel is at least its parent texel minus the one step-back of a hit (`len -= radius`,
+    compute.glsl:63), which is at most the child level's threshold."""
+    o = oracle.load("port")
+    for name in ("default_800x600", "eight_spheres_320x200"):
+        case = case_table[name]
+        lv, _ = _run(o, case)
+        n = len(lv)
+        W, H = float(case[3]), float(case[4])
+        for i in range(1, n):
+            child, parent = lv[i].astype(np.float64), lv[i - 1].astype(np.float64)
+            h, w = child.shape
+            ys, xs = np.mgrid[0:h, 0:w]
+            start = parent[ys >> 1, xs >> 1]
+            thr = float(np.float32(1.4142135) * np.float32(8) * o.image_size(n, i, W, H)[0])
+            # on a hit child - start = len_prev + last - (len_prev + 1) * thr >= -thr (thr < 1 on every level >= 1);
+            # 2e-3 covers the binary32 rounding of texels up to RENDER_DIST * 8
+            assert thr < 1.0
+            assert np.all(child >= start - thr - 2e-3), (name, i)
