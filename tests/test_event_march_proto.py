@@ -17,3 +17,18 @@ def test_event_driven_march_equals_eager_march_bit_for_bit():
     # the point of the design: almost no deferred work is ever replayed
     trips = sum(t["trips"] for t in tot.values())
     assert sum(t["replayed_objects"] for t in tot.values()) < 3 * trips
+
+
+def test_calendar_queue_march_equals_eager_march_bit_for_bit():
+    """Second step of the same design (tools/event_march_buckets.py): the objects live in a calendar queue over the absolute
+    ray length and a trip examines only the buckets within reach."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    spec = importlib.util.spec_from_file_location("event_march_buckets", os.path.join(ROOT, "tools", "event_march_buckets.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    bad, tot, n = mod.run(rays=2, delta=0.5, B=4096, seed=7)
+    assert bad == 0
+    trips = sum(t["trips"] for t in tot.values())
+    examined = sum(t["examined"] for t in tot.values())
+    assert examined < 400 * trips          # against 10,000 objects touched per trip by the eager form
