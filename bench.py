@@ -610,7 +610,8 @@ def run_ours(args, wl):
                     "dominant_kernel": dom, "step": step_roof}
     else:
         roofline = {"bound": "fp32_issue", "achieved": step_achieved / 1e12, "peak": fp32_peak * n_gpus / 1e12,
-                    "unit": "Tlane-op/s", "frac": step_achieved / (fp32_peak * n_gpus), "traffic": traffic,
+                    "unit": "Tlane-op/s", "frac": step_achieved / (fp32_peak * n_gpus),
+                    "traffic": None,   # the committed ncu capture is of the configs[1] strip launch, not of this workload
                     "peak_source": peak_note, "frac_of_nominal": step_achieved / (nominal * n_gpus),
                     "scope": "all launches of the step, gaps included (no single dominant launch was timed)",
                     "step": step_roof}
