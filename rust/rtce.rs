@@ -75,6 +75,15 @@ extern "C" {
     fn rtce_sync(ctx: *mut rtce_ctx) -> c_int;
     fn rtce_flush(ctx: *mut rtce_ctx) -> c_int;
     fn rtce_get_counters(ctx: *mut rtce_ctx, out: *mut Counters) -> c_int;
+    fn rtce_set_stream(ctx: *mut rtce_ctx, cuda_stream: *mut c_void) -> c_int;
+    fn rtce_trace_accumulate(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int) -> c_int;
+    fn rtce_readback_accum(ctx: *mut rtce_ctx, host: *mut f32, pitch_bytes: usize) -> c_int;
+    fn rtce_shade_batch(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int) -> c_int;
+    fn rtce_color_info(ctx: *const rtce_ctx, slot: c_int, w: *mut c_int, h: *mut c_int, device_rgba32f: *mut *mut f32) -> c_int;
+    fn rtce_readback_color(ctx: *mut rtce_ctx, slot: c_int, host_rgba32f: *mut f32) -> c_int;
+    fn rtce_readback_color_rgba8(ctx: *mut rtce_ctx, slot: c_int, host_rgba8: *mut u8) -> c_int;
+    fn rtce_host_alloc(out: *mut *mut c_void, nbytes: usize) -> c_int;
+    fn rtce_host_free(p: *mut c_void) -> c_int;
 }
 
 #[derive(Debug)]
@@ -167,6 +176,55 @@ impl ConeMarcher {
         self.check(st)
     }
 
+    /// Run the pass on a CUDA stream the caller owns (`cudaStream_t` as a pointer); null = the context's own stream.
+    pub fn set_stream(&mut self, cuda_stream: *mut c_void) -> Result<(), Error> {
+        let st = unsafe { rtce_set_stream(self.ctx, cuda_stream) };
+        self.check(st)
+    }
+
+    /// The render-pass half of `get_command_buffer` (src/main.rs:318-338: fullscreen triangle, one fragment per
+    /// window pixel running fragment.glsl:123-187) for the frames just traced with the same push constants.
+    /// Needs the materials and lights of `set_scene`.
+    pub fn shade_batch(&mut self, pcs: &[PushConstantData]) -> Result<(), Error> {
+        let st = unsafe { rtce_shade_batch(self.ctx, pcs.as_ptr(), pcs.len() as c_int) };
+        self.check(st)
+    }
+
+    /// The headless stand-in for presenting the swapchain image (src/main.rs:899-916): the shaded frame of `slot`
+    /// as RGBA8 UNORM, row-major, window size.
+    pub fn color_rgba8(&mut self, slot: i32) -> Result<(usize, usize, Vec<u8>), Error> {
+        let (mut w, mut h) = (0, 0);
+        let mut p: *mut f32 = std::ptr::null_mut();
+        let st = unsafe { rtce_color_info(self.ctx, slot, &mut w, &mut h, &mut p) };
+        self.check(st)?;
+        let mut out = vec![0u8; (w * h * 4) as usize];
+        let st = unsafe { rtce_readback_color_rgba8(self.ctx, slot, out.as_mut_ptr()) };
+        self.check(st)?;
+        Ok((w as usize, h as usize, out))
+    }
+
+    /// Labelled extension (no reference counterpart): FP32 running sum of the final level over `pcs` in frame order,
+    /// divided by the frame count; returns the accumulated image (final-level size).
+    pub fn trace_accumulate(&mut self, pcs: &[PushConstantData]) -> Result<(usize, usize, Vec<f32>), Error> {
+        let st = unsafe { rtce_trace_accumulate(self.ctx, pcs.as_ptr(), pcs.len() as c_int) };
+        self.check(st)?;
+        let (mut w, mut h) = (0, 0);
+        let mut p: *mut f32 = std::ptr::null_mut();
+        let st = unsafe { rtce_level_info(self.ctx, -1, 0, &mut w, &mut h, &mut p) };
+        self.check(st)?;
+        let mut out = vec![0f32; (w * h) as usize];
+        let st = unsafe { rtce_readback_accum(self.ctx, out.as_mut_ptr(), 0) };
+        self.check(st)?;
+        Ok((w as usize, h as usize, out))
+    }
+
+    /// Multi-GPU callers: restrict the pass to rows [y0, y1) x columns [x0, x1) of the final level and the ancestors
+    /// they touch (one context per GPU; a band traced alone equals the same rows of the whole image bit for bit).
+    pub fn set_rect(&mut self, x0: i32, y0: i32, x1: i32, y1: i32) -> Result<(), Error> {
+        let st = unsafe { rtce_set_rect(self.ctx, x0, y0, x1, y1) };
+        self.check(st)
+    }
+
     /// Order the context's stream after every batch traced so far (no host wait).
     pub fn flush(&mut self) -> Result<(), Error> {
         let st = unsafe { rtce_flush(self.ctx) };
@@ -178,4 +236,51 @@ impl Drop for ConeMarcher {
     fn drop(&mut self) {
         unsafe { rtce_destroy(self.ctx) }
     }
+}
+
+/// Pinned host memory for `render_to_host` targets (cudaHostAlloc behind the ABI, so the Rust side needs no CUDA crate).
+pub struct PinnedF32 {
+    ptr: *mut f32,
+    len: usize,
+}
+
+impl PinnedF32 {
+    pub fn new(len: usize) -> Result<Self, Error> {
+        let mut p: *mut c_void = std::ptr::null_mut();
+        let st = unsafe { rtce_host_alloc(&mut p, len * std::mem::size_of::<f32>()) };
+        if st != 0 {
+            let msg = unsafe { CStr::from_ptr(rtce_status_string(st)) }.to_string_lossy().into_owned();
+            return Err(Error { status: st, message: msg });
+        }
+        Ok(PinnedF32 { ptr: p as *mut f32, len })
+    }
+    pub fn as_slice(&self) -> &[f32] {
+        unsafe { std::slice::from_raw_parts(self.ptr, self.len) }
+    }
+    pub fn as_mut_ptr(&mut self) -> *mut f32 {
+        self.ptr
+    }
+}
+
+impl Drop for PinnedF32 {
+    fn drop(&mut self) {
+        unsafe {
+            rtce_host_free(self.ptr as *mut c_void);
+        }
+    }
+}
+
+/// Headless replacement of the reference's `main` loop body (src/main.rs:778-927 without window, swapchain and
+/// input): trace + shade one frame of the scene `mutable_data` (the bytes src/main.rs:524-605 builds) and return
+/// the RGBA8 image.  `rot` / `pos` are `data.rotation().to_array()` / `data.position.to_array()` (main.rs:770-773).
+pub fn render_headless(mutable_data: &[u8], width: f32, height: f32, fov: f32, render_dist: f32,
+                       rot: [f32; 4], pos: [f32; 3]) -> Result<(usize, usize, Vec<u8>), Error> {
+    let mut m = ConeMarcher::new(0, render_dist)?;
+    m.set_scene(mutable_data)?;
+    let cb = ConstantBuffer { view: [width, height], ratio: [fov, fov * height / width] };   // main.rs:608-611
+    m.set_view(&cb, 0)?;
+    let pc = PushConstantData { rot, pos, iter: 0, imageSize: [0.0; 2] };
+    m.trace(&pc)?;                                   // compute half, main.rs:291-316
+    m.shade_batch(std::slice::from_ref(&pc))?;       // render-pass half, main.rs:318-338
+    m.color_rgba8(0)
 }
