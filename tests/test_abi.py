@@ -89,3 +89,27 @@ def test_product_never_imports_oracle():
                 txt = open(os.path.join(dirpath, fn)).read()
                 assert not re.search(r"^\s*(import|from)\s+oracle\b", txt, flags=re.M), fn
                 assert not re.search(r"librtce_oracle|librtce_ref|#include\s+\"[^\"]*oracle", txt), fn
+
+
+def test_rust_binding_source_matches_the_header():
+    """rust/rtce.rs cannot be compiled here (no rustc): at least every extern it declares must exist in include/rtce.h
+    with the same number of parameters."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "rtce.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    c_fns = {}
+    for m in re.finditer(r"\b(rtce_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", hdr, flags=re.S):
+        args = m.group(2).strip()
+        c_fns[m.group(1)] = 0 if args in ("", "void") else args.count(",") + 1
+    rs = open(os.path.join(root, "rust", "rtce.rs")).read()
+    block = rs[rs.index('extern "C" {'):]
+    block = block[:block.index("\n}")]
+    block = re.sub(r"//.*", "", block)
+    n = 0
+    for m in re.finditer(r"fn\s+(rtce_[a-z0-9_]+)\s*\((.*?)\)\s*(->\s*[^;]+)?;", block, flags=re.S):
+        name, args = m.group(1), m.group(2).strip()
+        assert name in c_fns, f"{name} is not declared in include/rtce.h"
+        assert (args.count(",") + 1 if args else 0) == c_fns[name], name
+        n += 1
+    assert n >= 25
