@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define RTCE_ABI_VERSION 1
+#define RTCE_ABI_VERSION 2
 
 /* limits of the reference shader (utilities.glsl:1-3, compute.glsl:14-15, main.rs:359) */
 #define RTCE_REF_MAX_OBJECTS 8
@@ -88,45 +88,48 @@ typedef struct rtce_counters {
 } rtce_counters;
 
 typedef enum rtce_option {
-    RTCE_OPT_COUNTERS = 1,      /* 0/1: count R/E/S on the device (slower kernels; off by default) */
-    RTCE_OPT_FRAME_SLOTS = 2,   /* frames traced concurrently by rtce_trace_batch (pyramid replicas), default 16 */
-    RTCE_OPT_KERNEL = 3,        /* 0 = auto (= 3), 1 = per-pixel kernel per level, 2 = fused-pyramid kernel,
-                                   3 = strip kernel per large level + fused-pyramid kernel for the coarse levels */
+    RTCE_OPT_COUNTERS = 1,      /* 0/1: count R/E/S on the device (slower kernels, one lane, no graph replay; off by default) */
+    RTCE_OPT_FRAME_SLOTS = 2,   /* frames traced concurrently by rtce_trace_batch (pyramid replicas per window), default 16 */
+    RTCE_OPT_KERNEL = 3,        /* 0 = auto (= 3), 1 = per-pixel kernel per level (the second opinion of the parity tests),
+                                   3 = strip kernel per large level + one latency-oriented per-pixel launch per coarse level */
     RTCE_OPT_STRIP_MIN_RAYS = 4,/* kernel plan 3: a level is traced by the strip kernel when it has at least this
                                    many rays per launch (level pixels x frames of the launch), default 400000 */
-    RTCE_OPT_COARSE_FUSED = 6,  /* kernel plan 3, the levels below the strip threshold: 0 (default) = one latency-oriented
-                                   per-pixel launch per level, 1 = one fused-pyramid launch, 2 = ONE launch in which a
-                                   thread-block cluster per frame walks the levels with a cluster barrier in between
-                                   (fewest launches; measured slower on B200 at 1080p: a frame is confined to 8 SMs) */
+    RTCE_OPT_GROUPS = 5,        /* kernel plan 3: number of frame groups (1..8) a batch is split into; every group runs its
+                                   launch chain on its own stream so that latency-bound launches of one group overlap
+                                   issue-bound launches of the others.  0 (default) = auto: 2 in strict stream order,
+                                   1 when frames are in flight on several lanes (those already overlap) */
     RTCE_OPT_STRIP_ROWS = 7,    /* kernel plan 3: rows of a strip-kernel task (a task is 32 columns x this many rows), 1..32 */
-    RTCE_OPT_FRAMES_IN_FLIGHT = 9, /* 1..8, default 1.  The reference keeps frames in flight behind its swapchain
+    RTCE_OPT_GRAPH = 8,         /* kernel plan 3: 1 (default) = the launch chain of a frame batch (every level of every group,
+                                   forks and joins included) is captured once into a CUDA graph and replayed by later
+                                   calls with the same batch shape; the per-call cameras travel through device memory.
+                                   0 = issue every launch.  Counters and the debug timelines always issue every launch. */
+    RTCE_OPT_FRAMES_IN_FLIGHT = 9, /* 1..8, default 6.  The reference keeps frames in flight behind its swapchain
                                    (main.rs:859-884: acquire, submit, fence of the PREVIOUS frame).  With W > 1 successive
                                    rtce_trace_batch calls rotate over W windows of frame slots, each with its own streams:
                                    a call starts after everything enqueued on the context's stream so far, but NOT after
                                    the W-1 calls before it, so the latency-bound levels of one batch run under the
                                    issue-bound final level of another.  The context's stream is only ordered after the
                                    batch whose window the next call reuses; rtce_flush (stream-level) or rtce_sync /
-                                   rtce_readback* (host-level) order it after everything.  rtce_level_info and
-                                   rtce_readback address the window of the latest call.  W = 1 is strict stream order. */
+                                   rtce_readback* / rtce_shade_batch (which flush) order it after everything: a caller that
+                                   reads device pointers of rtce_level_info with its OWN kernels calls rtce_flush first.
+                                   rtce_level_info and rtce_readback address the window of the latest call.
+                                   W = 1 is strict stream order. */
     RTCE_OPT_STRIP_CTAS_PER_SM = 10, /* kernel plan 3: persistent CTAs per SM of a strip launch; 0 (default) = auto: every
-                                   resident slot (3 on B200) in strict stream order, 2 with two or three lanes in flight, 1 with more
+                                   resident slot in strict stream order, 2 with two or three lanes in flight, 1 with more
                                    (leaves room for the launches of the other lanes). */
     RTCE_OPT_FAR_MISS = 11,     /* kernel plan 3: 1 (default) = a ray whose parent texel lies beyond every sphere by more than
                                    RENDER_DIST (host-side conservative bound per camera) is resolved as start + RENDER_DIST
                                    without evaluating an SDF: exactly what compute.glsl:37-66 computes for it (all
                                    distances[i] >= RENDER_DIST -> one trip, no hit).  0 = evaluate every ray in full. */
-    RTCE_OPT_LARGE_KERNEL = 12, /* objCount > 8 (extension of utilities.glsl:3): 0 (default) = auto: the register kernel
-                                   (its capacity, 16384 spheres, is RTCE_MAX_SPHERES); 1 = shared-memory kernel (per-ray
-                                   cache of lower bounds as float4 groups in shared memory, any count that fits 200 KB);
-                                   2 = register kernel (the cache as an unrolled register array, 8 x G8 objects per thread). */
-    RTCE_OPT_GRAPH = 8,         /* kernel plan 3: 1 (default) = the launch chain of a frame batch (every level of every group,
-                                   forks and joins included) is captured once into a CUDA graph and replayed by later
-                                   calls with the same batch shape; the per-call cameras travel through device memory.
-                                   0 = issue every launch.  Counters and the debug timelines always issue every launch. */
-    RTCE_OPT_GROUPS = 5         /* kernel plan 3: number of frame groups (1..8) a batch is split into; every group runs its
-                                   launch chain on its own stream so that latency-bound launches of one group overlap
-                                   issue-bound launches of the others.  0 (default) = auto: 2 in strict stream order,
-                                   1 when frames are in flight on several lanes (those already overlap) */
+    RTCE_OPT_LARGE_KERNEL = 12, /* objCount > 8 (extension of utilities.glsl:3): 0 (default) = auto (the event-driven kernel);
+                                   2 = register kernel (per-ray cache of lower bounds as an unrolled register array, every
+                                   bound touched on every trip; the second opinion of the parity tests);
+                                   3 = event-driven kernel (per-ray bounds in a calendar over the ray length: a trip touches
+                                   only the objects that can be due or be the minimum).  Both hold RTCE_MAX_SPHERES. */
+    RTCE_OPT_MARCHER = 13       /* 3 (default) = tracing algorithm 3, the one compute.glsl:44-66 ships; 1, 2 = the author's
+                                   alternatives (shaders/tracing_algorithms.txt:2-13 and :16-37) dropped into the same
+                                   traceCone frame.  The reference holds only pseudo-code for 1 and 2: their checker is a
+                                   restatement, parity UNPINNED by the reference.  objCount 1..8, per-pixel kernels. */
 } rtce_option;
 
 /* -- lifetime ------------------------------------------------------------------------------
@@ -176,6 +179,11 @@ int rtce_trace_batch(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
  * is taken on the context's stream in frame order. */
 int rtce_trace_accumulate(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames);
 int rtce_accum_info(const rtce_ctx* ctx, int* w, int* h, float** device_ptr);
+/* Optional: do now what the first rtce_trace_batch (accumulate = 0) or rtce_trace_accumulate (accumulate = 1) of `frames`
+ * frames would do once — allocate the slot windows of every lane and capture + instantiate + upload the launch graphs
+ * of every chunk shape on every lane (command-buffer pre-recording; the reference re-records per frame, main.rs:284-289,
+ * 886).  Without it the first call of a shape pays for all lanes; no later call allocates or instantiates anything. */
+int rtce_prepare(rtce_ctx* ctx, int frames, int accumulate);
 
 /* -- consumers of binding 0 (main.rs:650-655 -> fragment.glsl:15,135) ---------------------------
  * Headless readback; both synchronise.  pitch_bytes = 0 -> tightly packed rows. */
@@ -200,6 +208,10 @@ int rtce_get_shade_counters(rtce_ctx* ctx, uint64_t out[4]);
  * and copy every frame's final level to `host_out` (frames * w * h floats), copies overlapped
  * with the tracing of later frames.  Synchronises before returning. */
 int rtce_render_to_host(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames, float* host_out);
+/* The headless replacement of one reference frame loop body (main.rs:886-914: compute half, render-pass half, present):
+ * trace `frames` frames, shade them (fragment.glsl) and copy every frame's RGBA8 UNORM image (window size, 4 bytes per
+ * pixel) to `host_rgba8` (frames * view_w * view_h * 4 bytes).  Synchronises before returning. */
+int rtce_render_rgba8_to_host(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames, unsigned char* host_rgba8);
 /* Page-locked host buffers for rtce_render_to_host / rtce_readback (pageable memory works, slower). */
 int rtce_host_alloc(void** out, size_t nbytes);
 int rtce_host_free(void* p);
@@ -216,6 +228,48 @@ int rtce_get_level_counters(rtce_ctx* ctx, int level, rtce_counters* out);
  * algorithm does for them (1 trip, objCount evaluations). */
 int rtce_get_far_miss_rays(rtce_ctx* ctx, int level, uint64_t* out);
 
+/* -- the step before the pass: camera -> push constants (main.rs:343-357, 402-414, 770-773) ------------
+ * Host arithmetic in binary32, one rounding per operation, in glam 0.21's operation order:
+ *   rtce_camera_rotation  Data::rotation (main.rs:402-404) = Quat::from_rotation_z(-yaw) * Quat::from_rotation_x(pitch),
+ *                         as Quat::to_array() = [x, y, z, w]; sin / cos of the half angles are libm sinf / cosf (glam calls
+ *                         f32::sin_cos), so the bits are those of THIS libm: parity with glam on the author's machine is
+ *                         unpinned (nothing to compare with: the Rust host cannot be built, SURVEY.md finding 6).
+ *   rtce_camera_pose      the per-frame update main.rs:770-773: pitch clamped to [-pi/2, pi/2], inout->rot = rotation,
+ *                         inout->pos += local_delta.x * right + local_delta.y * forward + local_delta.z * up with the axes
+ *                         (main.rs:351-357: right +X, forward +Y, up +Z) rotated by Quat::mul_vec3 (Data::position,
+ *                         main.rs:406-414).  local_delta = NULL adds nothing.  iter / imageSize are left alone. */
+int rtce_camera_rotation(float yaw, float pitch, float rot_xyzw[4]);
+int rtce_camera_pose(float yaw, float pitch, const float local_delta[3], rtce_push_constants* inout);
+
+/* -- several GPUs (no reference counterpart: one device, one queue, main.rs:450-460) ----------------------------------
+ * One process (or thread) per GPU, one context each.  The pass itself never communicates (a pixel depends only on its
+ * ancestor chain and uniforms, compute.glsl:81): every rank restricts itself to a row band with rtce_set_rect, and the
+ * ONE exchange is the gather of the accumulated image's bands to rank `dst`: grouped ncclSend / ncclRecv, every band
+ * received in place (a row band of a row-major image is contiguous).  NCCL is loaded on first use (dlopen of
+ * libnccl.so.2: a single-GPU caller needs no NCCL); the caller distributes the 128-byte unique id by its own means.
+ *   rtce_host_band_rows   equal split of `height` rows over `world` ranks in whole 8-row dispatch rows (compute.glsl:5)
+ *   rtce_gather_accum     stream-ordered after rtce_trace_accumulate: copies this rank's band out of the accumulator into
+ *                         one of two staging buffers and exchanges from there on the context's communication stream, so
+ *                         the gather of one step overlaps the tracing of the next.  bands = world x {y0, y1} final-level
+ *                         rows per rank (NULL = rtce_host_band_rows).  On `dst` the image lands in one of two gather
+ *                         buffers (rtce_gather_info, valid after rtce_gather_wait / rtce_readback_gathered).
+ *                         world = 1 (no rtce_comm_init needed): the band is copied, nothing is sent. */
+#define RTCE_COMM_ID_BYTES 128
+int rtce_comm_unique_id(void* id_out_128);
+int rtce_comm_init(rtce_ctx* ctx, const void* id_128, int rank, int world);
+int rtce_host_band_rows(int height, int world, int rank, int* y0, int* y1);
+int rtce_gather_accum(rtce_ctx* ctx, int dst, const int* bands);
+/* The frame-by-frame form: gathers the final-level row bands of frame slots 0 .. frames-1 of the LATEST batch to rank
+ * `dst`, every band received in place in `dst`'s own frame slots (whose other rows its kernels never write), so that
+ * rtce_level_info / rtce_readback on `dst` see whole frames.  Ordered after the batch; the window is not overwritten
+ * by a later batch before the exchange has read it; rtce_flush / rtce_sync / rtce_readback* wait for it. */
+int rtce_gather_frames(rtce_ctx* ctx, int dst, const int* bands, int frames);
+int rtce_gather_wait(rtce_ctx* ctx);   /* the context's stream waits (device side) for the gathers in flight */
+int rtce_gather_info(const rtce_ctx* ctx, int* w, int* h, float** device_ptr);
+int rtce_readback_gathered(rtce_ctx* ctx, float* host, size_t pitch_bytes);
+/* Device time of the most recent completed exchange (staging copy excluded), ms; synchronises the communication stream. */
+int rtce_gather_last_ms(rtce_ctx* ctx, float* ms);
+
 /* -- measurement support (no reference counterpart) ---------------------------------------------
  * Sustained FP32 CUDA-core issue rate of `device`: a register-only kernel of independent,
  * non-contracted FMUL/FADD chains, timed with CUDA events.  Writes lane-operations per second
@@ -225,6 +279,9 @@ int rtce_measure_fp32_issue(int device, int iters, double* lane_ops_per_s, doubl
  * sequences of the hot kernels return the bits of IEEE sqrt.rn / rcp.rn on their stated domains.
  * out4 = {sqrt mismatches, rcp mismatches, sqrt inputs checked, rcp inputs checked}. */
 int rtce_selftest_math(int device, uint64_t out4[4]);
+/* utilities.glsl:32-34 `repeat(p, r) = mod(p + 0.5 r, r) - 0.5 r` (unused by the reference's shaders, provided as a
+ * device function for completeness) evaluated on the GPU, componentwise, for n (p, r) pairs of host floats. */
+int rtce_selftest_repeat(int device, const float* p, const float* r, float* out, size_t n);
 
 /* Diagnostics: warp timeline of the strip-kernel launch that traces `level` (negative = from the last
  * level).  First call arms it; a later call copies 4 words per warp {start ns, tickets exhausted ns,

@@ -106,6 +106,18 @@ class Oracle:
             raise RuntimeError(f"oracle[{self.kind}] shade failed: {err}")
         return out, {"P": int(cnt[0]), "H": int(cnt[1]), "D": int(cnt[2]), "L": int(cnt[3])}
 
+    def repeat(self, p, r) -> np.ndarray:
+        """utilities.glsl:32-34 `repeat` on (n, 3) float32 arrays (the reference's own text for ref / refx)."""
+        p = np.ascontiguousarray(p, dtype=np.float32).reshape(-1, 3)
+        r = np.ascontiguousarray(r, dtype=np.float32).reshape(-1, 3)
+        out = np.empty_like(p)
+        prefix = _LIBS[self.kind][1]
+        fn = getattr(self.lib, f"{prefix}_repeat")
+        fn.restype = None
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]
+        fn(p.ctypes.data, r.ctypes.data, out.ctypes.data, p.shape[0])
+        return out
+
     def level_count(self, view_w: float, resize_rule: bool = False) -> int:
         return int(self._level_count(view_w, int(resize_rule)))
 

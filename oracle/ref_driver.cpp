@@ -59,6 +59,17 @@ RTCE_EXPORT void RTCE_FN(_image_size)(int levels, int i, float vw, float vh, flo
     rtce_hm_image_size(levels, i, vw, vh, out2);
 }
 
+// utilities.glsl:32-34 `repeat` — defined by the reference, called by none of its shaders; exposed so that the
+// device function can be compared with the reference's own text.  p3 / r3 / out3: n triples.
+RTCE_EXPORT void RTCE_FN(_repeat)(const float* p3, const float* r3, float* out3, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        const vec3 v = repeat(vec3(p3[3 * i], p3[3 * i + 1], p3[3 * i + 2]), vec3(r3[3 * i], r3[3 * i + 1], r3[3 * i + 2]));
+        out3[3 * i] = v.x;
+        out3[3 * i + 1] = v.y;
+        out3[3 * i + 2] = v.z;
+    }
+}
+
 // One frame of the pass.  spheres = n x {x,y,z,r}; level_out[i] = w_i*h_i floats
 // (row-major).  rect4 (final-level x0,y0,x1,y1) limits the work to that
 // rectangle's ancestor chain; NULL / all-zero = whole image.  counters3 (may be

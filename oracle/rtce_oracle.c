@@ -123,6 +123,18 @@ static float shade_pixel(uint32_t gx, uint32_t gy, uint32_t iter, const float im
     return f_max(len, 0.0f);                                 /* :86 */
 }
 
+/* utilities.glsl:32-34  repeat(p, r) = mod(p + 0.5*r, r) - 0.5*r, componentwise; GLSL mod(x, y) = x - y * floor(x / y)
+ * (spec 8.3).  Unused by the reference's shaders. */
+RTCE_EXPORT void rtce_oracle_repeat(const float* p3, const float* r3, float* out3, size_t n) {
+    for (size_t i = 0; i < 3 * n; i++) {
+        const float h = 0.5f * r3[i];
+        const float a = p3[i] + h;
+        const float q = a / r3[i];
+        const float m = a - r3[i] * floorf(q);
+        out3[i] = m - h;
+    }
+}
+
 RTCE_EXPORT int rtce_oracle_max_objects(void) { return 1 << 24; }
 RTCE_EXPORT int rtce_oracle_max_levels(void) { return RTCE_ORACLE_MAX_LEVELS; }
 RTCE_EXPORT float rtce_oracle_render_dist(void) { return 0.0f; /* any */ }

@@ -7,8 +7,10 @@ host-side mirror.  Nothing here imports `oracle/` and nothing computes the pass 
 """
 from .engine import (Engine, PinnedBuffer, RtceError, PUSH_CONSTANTS_DTYPE, make_push_constants, load_library,
                      host_level_count, host_level_dims, host_image_size, LIB_PATH, measure_fp32_issue, selftest_math,
-                     OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS, OPT_COARSE_FUSED, OPT_STRIP_ROWS, OPT_GRAPH, OPT_FRAMES_IN_FLIGHT, OPT_STRIP_CTAS_PER_SM, OPT_FAR_MISS, OPT_LARGE_KERNEL, KERNEL_AUTO, KERNEL_PER_LEVEL,
-                     KERNEL_FUSED, KERNEL_STRIP)
+                     OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS, OPT_STRIP_ROWS, OPT_GRAPH,
+                     OPT_FRAMES_IN_FLIGHT, OPT_STRIP_CTAS_PER_SM, OPT_FAR_MISS, OPT_LARGE_KERNEL, OPT_MARCHER, KERNEL_AUTO,
+                     KERNEL_PER_LEVEL, KERNEL_STRIP, LARGE_AUTO, LARGE_REGISTER, LARGE_EVENT, ABI_VERSION, selftest_repeat,
+                     camera_rotation, camera_pose, host_band_rows, comm_unique_id)
 from . import scene, camera
 
 __all__ = ["Engine", "PinnedBuffer", "RtceError", "PUSH_CONSTANTS_DTYPE", "make_push_constants", "load_library",

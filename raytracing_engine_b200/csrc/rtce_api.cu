@@ -1,6 +1,6 @@
-// rtce_api.cu — the C ABI declared in include/rtce.h: context, scene / view state, the level
-// loop of src/main.rs:291-316 expressed as kernel launches, and headless readback.
-// No CPU fallback exists anywhere in this file: every compute entry point launches CUDA kernels.
+// rtce_api.cu — the C ABI declared in include/rtce.h, first part: context lifetime, options, scene (binding 1)
+// and view (binding 2 + the pyramid of binding 0).  The pass loop lives in rtce_api_trace.cu.
+// No CPU fallback exists anywhere in the library: every compute entry point launches CUDA kernels.
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -11,120 +11,13 @@
 #include <string>
 #include <vector>
 
-#include "../../include/rtce.h"
-#include "rtce_host.hpp"
-#include "rtce_kernels.cuh"
+#include "rtce_ctx.hpp"
 
 using namespace rtce;
 
-static constexpr int kMaxGroups = 8;
-static constexpr unsigned kOverflowCap = 1u << 19;   // rays per frame group (38 MB each); beyond it long rays stay in their warp
+namespace rtce {
 
-// A lane is one self-contained launch chain: its own stream (plus one per frame group), its own
-// window of frame slots in the pyramid allocation, task counters, overflow queues, camera buffer
-// and captured graphs.  Lane 0 is the context's classic path.  With RTCE_OPT_FRAMES_IN_FLIGHT > 1
-// successive rtce_trace_batch calls rotate over the lanes and overlap on the device — the
-// latency-bound coarse levels and long-ray launches of one batch run under the issue-bound final
-// level of another — and rtce_trace_accumulate rotates its chunks the same way.
-static constexpr int kMaxLanes = 8;
-static constexpr int kCamRing = 8;
-struct ChunkGraph { int frames, slot0, lanes; uint64_t version; cudaGraphExec_t exec; uint64_t launches; };   // lanes: 0 = strict order
-struct Lane {
-    bool ready = false;
-    bool pending = false;                  // traced since the context's stream last waited for it
-    cudaStream_t st = nullptr;             // the lane's chain when it does not run on the context's stream
-    cudaStream_t grp_stream[kMaxGroups] = {};   // one per frame group of a chunk, forked from / joined to the chain's stream
-    cudaEvent_t ev_fork = nullptr, ev_join[kMaxGroups] = {};
-    cudaEvent_t ev_done = nullptr;         // last chunk traced
-    cudaEvent_t ev_free = nullptr;         // the consumer is done with the window
-    // Cameras of the chunk being traced.  The strip and coarse-level kernels read them from device memory, not
-    // from their parameters: their launch chain is replayed from a CUDA graph whose parameters are frozen.
-    Cam* d_cams = nullptr;                 // [kMaxBatch]
-    Cam* h_cams = nullptr;                 // pinned staging, [kCamRing][kMaxBatch]
-    cudaEvent_t ev_cam[kCamRing] = {};     // staging entry consumed
-    unsigned cam_seq = 0;
-    std::vector<ChunkGraph> graphs;
-    int* d_tickets = nullptr;    // [kMaxGroups][kMaxLevels][4] {task ticket, overflow count, overflow head, -}, zeroed per chunk
-    float* d_oq = nullptr;       // overflow queues of the strip launches (kMaxGroups x kOverflowCap rays x 18 words)
-};
-
-struct rtce_ctx {
-    int device = 0;
-    float render_dist = 1000.0f;
-    cudaStream_t own_stream = nullptr;   // created by rtce_create
-    cudaStream_t stream = nullptr;       // the stream work is issued on (own_stream or the caller's)
-    cudaStream_t copy_stream = nullptr;  // D2H copies of rtce_render_to_host
-    int groups = 0;                      // RTCE_OPT_GROUPS (0 = auto)
-    int coarse_mode = 0;                 // RTCE_OPT_COARSE_FUSED: 0 one launch per level, 1 fused-pyramid kernel, 2 cluster kernel
-    int strip_rows = 16;                 // RTCE_OPT_STRIP_ROWS
-    int strip_ctas_per_sm = 0;           // RTCE_OPT_STRIP_CTAS_PER_SM (0 = every resident slot)
-    int large_mode = 0;                  // RTCE_OPT_LARGE_KERNEL: 0 auto, 1 shared-memory kernel, 2 register kernel
-    bool far_cull = true;                // RTCE_OPT_FAR_MISS: resolve rays that start beyond every sphere without SDFs
-    // diagnostics (rtce_debug_launch_timeline): an event pair around every kernel launch
-    struct LaunchMark { cudaEvent_t e0, e1; int kind, level, group; };
-    bool mark_launches = false;
-    std::vector<LaunchMark> marks;
-    cudaEvent_t ev_traced[2] = {nullptr, nullptr};
-    cudaEvent_t ev_copied[2] = {nullptr, nullptr};
-    std::string err;
-
-    // binding 1 (MutableData.objCount / objs)
-    bool have_scene = false;
-    int n_spheres = 0;
-    float4 small[kSmallSceneMax];
-    float4* d_spheres = nullptr;   // objCount > 8 only
-    size_t d_spheres_cap = 0;
-
-    // binding 2 (ConstantBuffer) + binding 0 (the pyramid)
-    bool have_view = false;
-    rtce_constant_buffer cb{};
-    int levels = 0;
-    int lw[kMaxLevels]{}, lh[kMaxLevels]{};
-    size_t loff[kMaxLevels]{};   // float offset of each level inside one slot
-    size_t slot_stride = 0;      // floats per slot (all levels, 256-byte aligned each)
-    int slots = 16;
-    int slots_alloc = 0;
-    float* d_pyr = nullptr;
-    size_t d_pyr_floats = 0;
-    int rect[4] = {0, 0, 0, 0};
-    float* d_accum = nullptr;
-    size_t d_accum_floats = 0;
-
-    // presentation shading pass (fragment.glsl): the whole MutableData image, colour slots, staging
-    bool have_materials = false;             // rtce_set_scene was given the 656-byte image (rtce_set_spheres carries no materials / lights)
-    unsigned char md[RTCE_MUTABLE_DATA_SIZE] = {};
-    float4* d_color = nullptr;               // [slots][h][w] RGBA32F
-    size_t d_color_px = 0;                   // pixels per colour slot
-    int color_slots = 0;
-    uchar4* d_rgba8 = nullptr;               // one slot, for rtce_readback_color_rgba8
-    Cam* d_shade_cams = nullptr;             // [kMaxBatch]
-    Cam* h_shade_cams = nullptr;             // pinned
-    cudaEvent_t ev_shade_cams = nullptr;
-    unsigned long long* d_shade_counters = nullptr;   // {pixels, hit pixels, distance() calls, light evaluations}
-
-    // options / counters
-    bool count = false;
-    int kernel_mode = 0;
-    long long strip_min_rays = 400000;   // a level goes to the strip kernel when it has this many rays per launch
-    unsigned long long* d_counters = nullptr;
-    unsigned long long* d_dbg = nullptr;   // strip-kernel warp timeline of one level (rtce_debug_strip_timeline)
-    int dbg_level = -1;
-    // CUDA graphs of a chunk's launch chain (RTCE_OPT_GRAPH), valid while plan_version is unchanged
-    bool use_graph = true;
-    uint64_t plan_version = 1;             // bumped by every setter that changes what a launch chain looks like
-    // lanes: independent launch chains over their own window of frame slots (see Lane)
-    Lane lanes[kMaxLanes];
-    int in_flight = 1;                     // RTCE_OPT_FRAMES_IN_FLIGHT
-    int next_lane = 0, last_lane = 0;
-    int lanes_active = 1;                  // lanes the current call rotates over
-    int windows_alloc = 0;                 // slot windows the pyramid allocation holds
-    cudaEvent_t ev_user = nullptr;         // "everything the caller enqueued so far" on `stream`
-    uint64_t launches = 0;
-};
-
-namespace {
-
-int fail(rtce_ctx* c, int code, const char* what, cudaError_t e = cudaSuccess) {
+int fail(rtce_ctx* c, int code, const char* what, cudaError_t e) {
     if (c) {
         c->err = what;
         if (e != cudaSuccess) {
@@ -134,24 +27,6 @@ int fail(rtce_ctx* c, int code, const char* what, cudaError_t e = cudaSuccess) {
     }
     return code;
 }
-
-#define RTCE_CUDA(c, call)                                            \
-    do {                                                              \
-        cudaError_t e_ = (call);                                      \
-        if (e_ != cudaSuccess) return fail((c), RTCE_ERR_CUDA, #call, e_); \
-    } while (0)
-
-struct DeviceGuard {
-    int prev = -1;
-    explicit DeviceGuard(int dev) {
-        cudaGetDevice(&prev);
-        if (prev != dev) cudaSetDevice(dev);
-        else prev = -1;
-    }
-    ~DeviceGuard() {
-        if (prev >= 0) cudaSetDevice(prev);
-    }
-};
 
 // Allocate what lane `l` needs (idempotent).
 int lane_init(rtce_ctx* c, int l) {
@@ -201,6 +76,8 @@ void lane_free(Lane& L) {
 // Make the context's stream wait for every lane that has traced since it last did (stream-level, the host
 // does not block): after this, work enqueued on the context's stream sees every image traced so far.
 int flush_lanes(rtce_ctx* c) {
+    int r = comm_wait_all(c, c->stream);   // frames / bands still travelling between ranks
+    if (r) return r;
     for (int l = 0; l < kMaxLanes; l++) {
         Lane& L = c->lanes[l];
         if (L.ready && L.pending) {
@@ -220,7 +97,7 @@ int quiesce(rtce_ctx* c) {
 }
 
 // The pyramid allocation holds `windows` windows of c->slots frame slots (window w belongs to lane w).
-int ensure_pyramid(rtce_ctx* c, int windows = 1) {
+int ensure_pyramid(rtce_ctx* c, int windows) {
     windows = std::max(windows, std::max(1, c->windows_alloc));   // never shrink: a lane's graphs point into its window
     const size_t need = c->slot_stride * (size_t)c->slots * (size_t)windows;
     if (c->d_pyr && c->d_pyr_floats >= need && c->slots_alloc == c->slots && c->windows_alloc >= windows) return RTCE_OK;
@@ -248,12 +125,7 @@ int ensure_pyramid(rtce_ctx* c, int windows = 1) {
     return RTCE_OK;
 }
 
-// First float of frame slot `slot` of window `w`.
-inline float* window_slot(const rtce_ctx* c, int w, int slot) {
-    return c->d_pyr + ((size_t)w * (size_t)c->slots + (size_t)slot) * c->slot_stride;
-}
-
-}  // namespace
+}  // namespace rtce
 
 extern "C" {
 
@@ -288,9 +160,17 @@ int rtce_create(int device, float render_dist, rtce_ctx** out) {
     if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_user, cudaEventDisableTiming) != cudaSuccess ||
-        cudaMalloc(&c->d_counters, 4 * kMaxLevels * sizeof(unsigned long long)) != cudaSuccess || lane_init(c, 0) != RTCE_OK) {
+        cudaMalloc(&c->d_counters, 4 * kMaxLevels * sizeof(unsigned long long)) != cudaSuccess) {
         rtce_destroy(c);
         return RTCE_ERR_CUDA;
+    }
+    // every lane the default options can use exists from the start: no stream / event creation and no
+    // cudaMalloc happens inside a later rtce_trace* call
+    for (int l = 0; l < std::max(c->in_flight, kAccumLanes); l++) {
+        if (lane_init(c, l) != RTCE_OK) {
+            rtce_destroy(c);
+            return RTCE_ERR_CUDA;
+        }
     }
     for (int i = 0; i < 2; i++) {
         cudaEventCreateWithFlags(&c->ev_traced[i], cudaEventDisableTiming);
@@ -306,7 +186,9 @@ void rtce_destroy(rtce_ctx* c) {
     DeviceGuard g(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     if (c->copy_stream) cudaStreamSynchronize(c->copy_stream);
+    comm_destroy(c);
     for (int l = 0; l < kMaxLanes; l++) lane_free(c->lanes[l]);
+    if (c->large_state) cudaFree(c->large_state);
     if (c->ev_user) cudaEventDestroy(c->ev_user);
     for (int i = 0; i < 2; i++) {
         if (c->ev_traced[i]) cudaEventDestroy(c->ev_traced[i]);
@@ -341,6 +223,17 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             if (value < 1 || value > kMaxLanes) return fail(c, RTCE_ERR_INVALID, "frames in flight out of range");
             c->in_flight = (int)value;
             c->next_lane = 0;
+            {
+                DeviceGuard g(c->device);
+                for (int l = 0; l < std::max(c->in_flight, kAccumLanes); l++) {
+                    int r = lane_init(c, l);
+                    if (r) return r;
+                }
+                if (c->have_view) {   // the windows of the new lanes, now rather than inside the next trace call
+                    int r = ensure_pyramid(c, c->in_flight);
+                    if (r && r != RTCE_ERR_NOMEM) return r;
+                }
+            }
             return RTCE_OK;
         case RTCE_OPT_GRAPH: c->use_graph = value != 0; return RTCE_OK;
         case RTCE_OPT_COUNTERS: c->count = value != 0; return RTCE_OK;
@@ -353,7 +246,7 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             }
             return RTCE_OK;
         case RTCE_OPT_KERNEL:
-            if (value < 0 || value > 3) return fail(c, RTCE_ERR_INVALID, "kernel mode out of range");
+            if (value != 0 && value != 1 && value != 3) return fail(c, RTCE_ERR_INVALID, "kernel plan: 0 auto, 1 per-pixel, 3 strip");
             c->kernel_mode = (int)value;
             return RTCE_OK;
         case RTCE_OPT_STRIP_ROWS:
@@ -362,16 +255,16 @@ int rtce_set_option(rtce_ctx* c, int option, int64_t value) {
             return RTCE_OK;
         case RTCE_OPT_FAR_MISS: c->far_cull = value != 0; return RTCE_OK;
         case RTCE_OPT_LARGE_KERNEL:
-            if (value < 0 || value > 2) return fail(c, RTCE_ERR_INVALID, "large-scene kernel out of range");
+            if (value != 0 && value != 2 && value != 3) return fail(c, RTCE_ERR_INVALID, "large-scene kernel: 0 auto, 2 register, 3 event-driven");
             c->large_mode = (int)value;
             return RTCE_OK;
         case RTCE_OPT_STRIP_CTAS_PER_SM:
             if (value < 0 || value > 8) return fail(c, RTCE_ERR_INVALID, "strip CTAs per SM out of range");
             c->strip_ctas_per_sm = (int)value;
             return RTCE_OK;
-        case RTCE_OPT_COARSE_FUSED:
-            if (value < 0 || value > 2) return fail(c, RTCE_ERR_INVALID, "coarse plan out of range");
-            c->coarse_mode = (int)value;
+        case RTCE_OPT_MARCHER:
+            if (value < 1 || value > 3) return fail(c, RTCE_ERR_INVALID, "marcher: 1, 2 or 3");
+            c->marcher = (int)value;
             return RTCE_OK;
         case RTCE_OPT_GROUPS:
             if (value < 0 || value > kMaxGroups) return fail(c, RTCE_ERR_INVALID, "groups out of range");
@@ -491,6 +384,12 @@ int rtce_set_view(rtce_ctx* c, const rtce_constant_buffer* cb, int levels) {
     c->slot_stride = off;
     c->rect[0] = c->rect[1] = c->rect[2] = c->rect[3] = 0;
     c->have_view = true;
+    if (c->d_accum) {   // the accumulator belongs to the old geometry
+        RTCE_CUDA(c, cudaFree(c->d_accum));
+        c->d_accum = nullptr;
+        c->d_accum_floats = 0;
+        c->accum_rows[0] = c->accum_rows[1] = -1;
+    }
     if (!same) {
         c->d_pyr_floats = 0;   // force re-allocation (and the clear)
         if (c->d_pyr) {
@@ -498,7 +397,10 @@ int rtce_set_view(rtce_ctx* c, const rtce_constant_buffer* cb, int levels) {
             c->d_pyr = nullptr;
         }
     }
-    return ensure_pyramid(c);
+    // the slot windows of every lane in flight are allocated here, not inside the first trace call
+    r = ensure_pyramid(c, c->in_flight);
+    if (r == RTCE_ERR_NOMEM) r = ensure_pyramid(c, 1);
+    return r;
 }
 
 int rtce_set_rect(rtce_ctx* c, int x0, int y0, int x1, int y1) {
@@ -535,4 +437,3 @@ int rtce_level_info(const rtce_ctx* c, int level, int slot, int* w, int* h, floa
 
 }  // extern "C"
 
-#include "rtce_api_trace.inc"

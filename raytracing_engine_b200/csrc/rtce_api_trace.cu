@@ -1,5 +1,14 @@
-// rtce_api_trace.inc — second half of rtce_api.cu: the pass loop (src/main.rs:291-316) and the
-// consumers of binding 0.  Included by rtce_api.cu (same translation unit).
+// rtce_api_trace.cu — the C ABI declared in include/rtce.h, second part: the pass loop (src/main.rs:291-316)
+// expressed as kernel launches / replayed launch graphs, and the consumers of binding 0 (headless readback,
+// the presentation shading pass).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+#include "rtce_ctx.hpp"
+
+using namespace rtce;
 
 namespace {
 
@@ -22,48 +31,16 @@ struct MarkScope {
     }
 };
 
-// Fill the fused-kernel parameters for levels [0, nlev) of the current view / rect / scene (cameras
-// excluded).  nlev == c->levels is the whole pyramid; a shorter prefix is itself a pyramid whose
-// finest level is nlev-1 (every level carries its own imageSize), used for the coarse levels that
-// are too small for the strip kernel.
-void fill_fused(const rtce_ctx* c, FusedParams& F, int nlev) {
-    const int n = c->levels;
-    int fr[4];
-    host_level_rect(n, nlev - 1, c->rect, c->lw[nlev - 1], c->lh[nlev - 1], fr);
-    F.slot_stride = c->slot_stride;
-    F.counters = c->d_counters + 4 * (nlev - 1);   // a fused launch books all its levels under its finest one
-    F.levels = nlev;
-    F.n_spheres = c->n_spheres;
-    F.gx0 = fr[0] & ~(kFusedTile - 1);
-    F.gy0 = fr[1] & ~(kFusedTile - 1);
-    F.ntx = (fr[2] - F.gx0 + kFusedTile - 1) / kFusedTile;
-    F.nty = (fr[3] - F.gy0 + kFusedTile - 1) / kFusedTile;
-    F.ratx = c->cb.ratio[0];
-    F.raty = c->cb.ratio[1];
-    F.render_dist = c->render_dist;
-    for (int i = 0; i < nlev; i++) {
-        float isz[2];
-        host_image_size(n, i, c->cb.view[0], c->cb.view[1], isz);
-        int rc[4];
-        host_level_rect(n, i, c->rect, c->lw[i], c->lh[i], rc);
-        FusedLevel& L = F.lv[i];
-        L.off = c->loff[i];
-        L.isx = isz[0];
-        L.isy = isz[1];
-        L.threshold = host_threshold(isz[0]);
-        L.w = c->lw[i];
-        L.h = c->lh[i];
-        L.rx0 = rc[0]; L.ry0 = rc[1]; L.rx1 = rc[2]; L.ry1 = rc[3];
-    }
-    memcpy(F.sph, c->small, sizeof(F.sph));
-}
-
 // Far-miss distance of a camera (Cam::pad): a ray whose parent texel is at least this far starts beyond every
 // sphere by more than RENDER_DIST, so every distances[i] of compute.glsl:37-39 is >= RENDER_DIST, the first march
 // trip takes dist = RENDER_DIST (:49, :56), is no hit (:62, RENDER_DIST > threshold) and ends the loop (:44):
 // the texel is start + RENDER_DIST without evaluating a single SDF.  distances[i] = |pos + dir start - c_i| - r_i
 // >= start |dir| - (|pos - c_i| + r_i); the bound below keeps a 0.1 % + 1 margin over the ~1e-6 relative rounding
-// of the computed value (|dir| = 1 +- 3e-7).  +inf disables the shortcut.
+// of the computed value (|dir| = 1 +- 3e-7), plus a term for the rounding of origin = pos + dir * start itself, which
+// scales with the COORDINATES (half an ulp of |pos| + start per component), not with the distances: a camera at 1e8
+// with a sphere 10 units away has k ~ 10 but an origin known only to +- 8.  The bound is a fixed point of
+// t = base + u (|pos|_inf + t) with u = 1e-6 (> sqrt(3) * 2^-23 * 1.5, three components, generous).  +inf disables
+// the shortcut.
 float far_miss_distance(const rtce_ctx* c, const float pos[3]) {
     const float inf = std::numeric_limits<float>::infinity();
     if (!(c->render_dist > 0.0f) || c->n_spheres > kSmallSceneMax) return inf;
@@ -79,8 +56,10 @@ float far_miss_distance(const rtce_ctx* c, const float pos[3]) {
         if (!(d <= 1e30)) return inf;
         k = std::max(k, d);
     }
-    const double t = 1.001 * ((double)c->render_dist + k) + 1.0;
-    if (!(t < 1e30)) return inf;
+    const double pinf = std::max(std::fabs((double)pos[0]), std::max(std::fabs((double)pos[1]), std::fabs((double)pos[2])));
+    const double u = 1.0e-6;
+    const double t = (1.001 * ((double)c->render_dist + k) + 1.0 + u * pinf) / (1.0 - u);
+    if (!(t < 1e30) || !(pinf < 1e30)) return inf;
     return std::nextafter((float)t, inf);
 }
 
@@ -92,33 +71,13 @@ void fill_cams(const rtce_ctx* c, Cam* cams, const rtce_push_constants* pcs, int
     }
 }
 
-// Levels [0, nlev) in ONE launch of the fused-pyramid kernel.  Returns 1 when launched, 0 when the
-// geometry does not fit its shared-memory regions, < 0 on error.
-int launch_fused_prefix(rtce_ctx* c, const Cam* cams, int frames, float* base, int nlev, cudaStream_t st) {
-    FusedParams F{};
-    fill_fused(c, F, nlev);
-    if (!fused_geometry_ok(F)) return 0;
-    F.base = base;
-    memcpy(F.cam, cams, sizeof(Cam) * (size_t)frames);
-    MarkScope mark(c, st, 10, nlev - 1, -1);
-    cudaError_t e = launch_trace_fused(F, frames, c->count, st);   // main.rs:300-316 in one launch
-    if (e != cudaSuccess) return fail(c, RTCE_ERR_CUDA, "fused kernel launch", e);
-    c->launches++;
-    return 1;
-}
-
-bool fused_prefix_fits(const rtce_ctx* c, int nlev) {
-    FusedParams F{};
-    fill_fused(c, F, nlev);
-    return fused_geometry_ok(F);
-}
-
 // One level (main.rs:301-314: push constants {iter, imageSize} + dispatch) with the kernel `kind`:
 // 0 = per-pixel kernel, 1 = strip kernel, 2 = large-scene kernel, 3 = latency-oriented per-pixel kernel.
 // `g` selects the group's ticket block / overflow queue (strip kernel only), `st` the stream.
 // `cams` are the frames' cameras on the host, `dcams` the same in device memory.
+// `crowd` = how many lanes trace side by side (0 or 1: this chain has the device to itself).
 int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int frames, float* base, int i, int kind, cudaStream_t st,
-                 int g, int share = 1, bool lanes_in_flight = false) {
+                 int g, int share = 1, int crowd = 0) {
     int* const tickets = L.d_tickets + (size_t)g * kMaxLevels * 4;
     float isz[2];
     host_image_size(c->levels, i, c->cb.view[0], c->cb.view[1], isz);   // main.rs:303-305
@@ -147,7 +106,7 @@ int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int fr
         S.cta_share = share;
         // auto: with several lanes in flight a strip launch takes one CTA per SM (two with 2-3 lanes), so that the launches of the
         // other lanes (strips included) find room beside it; alone it takes every resident slot
-        S.ctas_per_sm = c->strip_ctas_per_sm > 0 ? c->strip_ctas_per_sm : (lanes_in_flight ? (c->lanes_active >= 4 ? 1 : 2) : 0);
+        S.ctas_per_sm = c->strip_ctas_per_sm > 0 ? c->strip_ctas_per_sm : (crowd > 1 ? (crowd >= 4 ? 1 : 2) : 0);
         S.nty = (rc[3] - rc[1] + rows - 1) / rows;
         S.frames = frames;
         S.n_spheres = c->n_spheres;
@@ -215,10 +174,8 @@ int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int fr
         G.threshold = host_threshold(isz[0]);
         G.render_dist = c->render_dist;
         memcpy(G.cam, cams, sizeof(Cam) * (size_t)frames);
-        const bool reg = c->large_mode == 2 || (c->large_mode == 0 && c->n_spheres <= large_reg_capacity());
-        if (reg && c->n_spheres > large_reg_capacity())
-            return fail(c, RTCE_ERR_INVALID, "RTCE_OPT_LARGE_KERNEL = 2: too many spheres for the register kernel");
-        e = reg ? launch_trace_level_large_reg(G, frames, c->count, st) : launch_trace_level_large(G, frames, c->count, st);
+        if (c->n_spheres > large_reg_capacity()) return fail(c, RTCE_ERR_LIMIT, "more spheres than RTCE_MAX_SPHERES");
+        e = launch_trace_level_large_reg(G, frames, c->count, st);
     }
     if (e != cudaSuccess) return fail(c, RTCE_ERR_CUDA, "kernel launch", e);
     c->launches++;
@@ -228,36 +185,37 @@ int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int fr
 // Trace `frames` (<= min(slots, kMaxBatch)) frames into slots [slot0, slot0 + frames): the level
 // loop of main.rs:300-316.  Kernel plan (RTCE_OPT_KERNEL):
 //   strip (auto)  levels with >= strip_min_rays rays per launch -> one strip-kernel launch (+ its
-//                 overflow launch) each; the coarse levels below them -> one fused-pyramid launch.
-//                 The frames are split in RTCE_OPT_GROUPS groups that run the same launch chain on
-//                 their own streams (forked from / joined to the context's stream), and a strip
+//                 overflow launch) each; the coarse levels below them -> one latency-oriented per-pixel
+//                 launch each.  The frames are split in RTCE_OPT_GROUPS groups that run the same launch
+//                 chain on their own streams (forked from / joined to the chain's stream), and a strip
 //                 launch takes only a share of the CTA slots: the coarse levels, the overflow
 //                 launches and the ragged end of every launch are latency-bound (a grazing cone
 //                 marches ~100 dependent trips), so the machine is kept busy by whichever groups
 //                 are in an issue-bound launch at the moment.
-//   fused         the whole pyramid in one fused-pyramid launch
-//   per-level     one per-pixel kernel launch per level (also the fallback when a geometry does not fit)
+//   per-level     one per-pixel kernel launch per level (RTCE_OPT_KERNEL = 1, RENDER_DIST <= 0, marchers 1 / 2)
 //   objCount > 8  one large-scene kernel launch per level
 bool strip_plan(const rtce_ctx* c) {   // the strip kernel assumes RENDER_DIST > 0
-    return c->n_spheres <= kSmallSceneMax && (c->kernel_mode == 0 || c->kernel_mode == 3) && c->render_dist > 0.0f;
+    return c->n_spheres <= kSmallSceneMax && (c->kernel_mode == 0 || c->kernel_mode == 3) && c->render_dist > 0.0f &&
+           c->marcher == 3;
 }
 
 // The launch chain of one chunk; `cams` (host) go into the parameters of the kernels that take them
-// there, c->d_cams (already uploaded) is read by the strip-plan kernels.
-int emit_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const Cam* cams, int frames, int slot0) {
+// there, the lane's d_cams (already uploaded) is read by the strip-plan kernels.
+int emit_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const Cam* cams, int frames, int slot0, int crowd) {
     Lane& L = c->lanes[lane];
     const Cam* dcams = L.d_cams;
     float* base = window_slot(c, lane, slot0);
     int r;
     if (c->n_spheres > kSmallSceneMax) {
+        if (c->marcher != 3) return fail(c, RTCE_ERR_INVALID, "RTCE_OPT_MARCHER 1 / 2 need objCount <= 8");
         for (int i = 0; i < c->levels; i++)
             if ((r = launch_level(c, L, cams, dcams, frames, base, i, 2, ls, 0))) return r;
         return RTCE_OK;
     }
     if (strip_plan(c)) {
         // frame groups: contiguous frame ranges, sizes differ by at most one
-        // groups: auto = 2 in strict stream order, 1 when several lanes are in flight (the lanes already overlap)
-        const int want = c->groups > 0 ? c->groups : (ls != c->stream ? 1 : 2);
+        // groups: auto = 2 when this chain has the device to itself, 1 when several lanes trace side by side (they already overlap)
+        const int want = c->groups > 0 ? c->groups : (crowd > 1 ? 1 : 2);
         const int ng = std::max(1, std::min(want, frames));
         int nf[kMaxGroups], f0[kMaxGroups];
         for (int g = 0, f = 0; g < ng; g++) {
@@ -274,8 +232,8 @@ int emit_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const Cam* cams, int fram
             if ((unsigned long long)nf[0] * c->slot_stride >= (1ull << 32)) break;   // strip queue offsets are 32-bit
             k--;
         }
-        // With one group the launches run on the context's stream; with several, every group has
-        // its own stream, forked from and joined to the context's stream.
+        // With one group the launches run on the chain's stream; with several, every group has
+        // its own stream, forked from and joined to the chain's stream.
         cudaStream_t st[kMaxGroups];
         for (int g = 0; g < ng; g++) st[g] = ng == 1 ? ls : L.grp_stream[g];
         if (ng > 1) {
@@ -289,35 +247,14 @@ int emit_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const Cam* cams, int fram
             if (k < c->levels)   // task counters / overflow cursors of this group's strip launches
                 RTCE_CUDA(c, cudaMemsetAsync(L.d_tickets + (size_t)g * kMaxLevels * 4, 0, sizeof(int) * kMaxLevels * 4, st[g]));
         }
-        if (k > 0 && c->coarse_mode == 2) {   // the coarse levels: one cluster-kernel launch per group
-            FusedParams F{};
-            fill_fused(c, F, k);
-            for (int g = 0; g < ng; g++) {
-                F.base = base + (size_t)f0[g] * c->slot_stride;
-                F.cams = dcams + f0[g];
-                MarkScope mark(c, st[g], 4, k - 1, g);
-                cudaError_t e = launch_trace_coarse(F, nf[g], c->count, st[g]);
-                if (e != cudaSuccess) return fail(c, RTCE_ERR_CUDA, "coarse cluster kernel launch", e);
-                c->launches++;
-            }
-        }
-        for (int i = 0; i < k && c->coarse_mode != 2; i++) {   // the coarse levels, other plans
-            for (int g = 0; g < ng; g++) {
-                float* gb = base + (size_t)f0[g] * c->slot_stride;
-                if (i == 0 && c->coarse_mode == 1) {
-                    r = launch_fused_prefix(c, cams + f0[g], nf[g], gb, k, st[g]);
-                    if (r < 0) return r;
-                    if (r > 0) continue;
-                } else if (c->coarse_mode == 1 && fused_prefix_fits(c, k)) {
-                    continue;
-                }
-                if ((r = launch_level(c, L, cams + f0[g], dcams + f0[g], nf[g], gb, i, 3, st[g], g, share))) return r;
-            }
-        }
+        for (int i = 0; i < k; i++)   // the coarse levels
+            for (int g = 0; g < ng; g++)
+                if ((r = launch_level(c, L, cams + f0[g], dcams + f0[g], nf[g], base + (size_t)f0[g] * c->slot_stride, i, 3, st[g], g, share)))
+                    return r;
         for (int i = k; i < c->levels; i++)
             for (int g = 0; g < ng; g++)
                 if ((r = launch_level(c, L, cams + f0[g], dcams + f0[g], nf[g], base + (size_t)f0[g] * c->slot_stride, i, 1, st[g], g, share,
-                                      ls != c->stream)))
+                                      crowd)))
                     return r;
         if (ng > 1) {
             for (int g = 0; g < ng; g++) {
@@ -327,32 +264,16 @@ int emit_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const Cam* cams, int fram
         }
         return RTCE_OK;
     }
-    if (c->kernel_mode == 2) {
-        r = launch_fused_prefix(c, cams, frames, base, c->levels, ls);
-        if (r < 0) return r;
-        if (r == 0) return fail(c, RTCE_ERR_LIMIT, "fused kernel: view / rect geometry does not fit; use RTCE_OPT_KERNEL 0, 1 or 3");
-        return RTCE_OK;
-    }
     for (int i = 0; i < c->levels; i++)
         if ((r = launch_level(c, L, cams, dcams, frames, base, i, 0, ls, 0))) return r;
     return RTCE_OK;
 }
 
-// Trace one chunk on lane `lane`, whose chain runs on stream `ls`: stage its cameras (pinned ring ->
-// the lane's device buffer, stream-ordered), then either issue the launch chain or — strip plan, no
-// counters / diagnostics — replay the CUDA graph captured from it (RTCE_OPT_GRAPH): ~90 launches on
-// up to 8 streams cost one graph launch on the host.
-int trace_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const rtce_push_constants* pcs, int frames, int slot0) {
-    Lane& L = c->lanes[lane];
-    const int ring = (int)(L.cam_seq++ % kCamRing);
-    RTCE_CUDA(c, cudaEventSynchronize(L.ev_cam[ring]));   // the copy that last used this entry is done
-    Cam* cams = L.h_cams + (size_t)ring * kMaxBatch;
-    fill_cams(c, cams, pcs, frames);
-    RTCE_CUDA(c, cudaMemcpyAsync(L.d_cams, cams, sizeof(Cam) * (size_t)frames, cudaMemcpyHostToDevice, ls));
-    RTCE_CUDA(c, cudaEventRecord(L.ev_cam[ring], ls));
-    const bool graphable = c->use_graph && strip_plan(c) && c->coarse_mode != 1 && !c->count && !c->mark_launches &&
-                           c->dbg_level < 0;
-    if (!graphable) return emit_chunk(c, lane, ls, cams, frames, slot0);
+bool graphable(const rtce_ctx* c) {
+    return c->use_graph && strip_plan(c) && !c->count && !c->mark_launches && c->dbg_level < 0;
+}
+
+void drop_stale_graphs(rtce_ctx* c, Lane& L) {
     for (auto it = L.graphs.begin(); it != L.graphs.end();) {
         if (it->version != c->plan_version) {
             cudaGraphExecDestroy(it->exec);
@@ -361,33 +282,85 @@ int trace_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const rtce_push_constant
             ++it;
         }
     }
-    for (const auto& g : L.graphs) {
-        if (g.frames == frames && g.slot0 == slot0 && g.lanes == (ls != c->stream ? c->lanes_active : 0)) {
-            RTCE_CUDA(c, cudaGraphLaunch(g.exec, ls));
-            c->launches += g.launches;
-            return RTCE_OK;
-        }
-    }
+}
+
+const ChunkGraph* find_graph(const Lane& L, int frames, int slot0, int crowd) {
+    for (const auto& g : L.graphs)
+        if (g.frames == frames && g.slot0 == slot0 && g.lanes == crowd) return &g;
+    return nullptr;
+}
+
+// Capture, instantiate and upload the launch graph of chunk shape (frames, slot0, crowd) on lane `lane`, whose
+// chain runs on `ls` (idempotent).  The camera values are not part of the graph: they travel through the lane's
+// device buffer, so the capture needs no cameras (the kernels that take them in their parameters are not
+// graphable plans).
+int capture_graph(rtce_ctx* c, int lane, cudaStream_t ls, int frames, int slot0, int crowd) {
+    Lane& L = c->lanes[lane];
+    drop_stale_graphs(c, L);
+    if (find_graph(L, frames, slot0, crowd)) return RTCE_OK;
     const uint64_t l0 = c->launches;
+    Cam dummy[kMaxBatch] = {};
     RTCE_CUDA(c, cudaStreamBeginCapture(ls, cudaStreamCaptureModeRelaxed));
-    const int r = emit_chunk(c, lane, ls, cams, frames, slot0);
+    const int r = emit_chunk(c, lane, ls, dummy, frames, slot0, crowd);
     cudaGraph_t graph = nullptr;
     const cudaError_t ec = cudaStreamEndCapture(ls, &graph);
+    const uint64_t n_launch = c->launches - l0;
+    c->launches = l0;   // a capture launches nothing
     if (r || ec != cudaSuccess) {
         if (graph) cudaGraphDestroy(graph);
         cudaGetLastError();
         return r ? r : fail(c, RTCE_ERR_CUDA, "cudaStreamEndCapture", ec);
     }
-    ChunkGraph cg{frames, slot0, ls != c->stream ? c->lanes_active : 0, c->plan_version, nullptr, c->launches - l0};
+    ChunkGraph cg{frames, slot0, crowd, c->plan_version, nullptr, n_launch};
     const cudaError_t ei = cudaGraphInstantiate(&cg.exec, graph, 0);
     cudaGraphDestroy(graph);
     if (ei != cudaSuccess) return fail(c, RTCE_ERR_CUDA, "cudaGraphInstantiate", ei);
-    if (L.graphs.size() >= 16) {   // a caller cycling through many chunk shapes: start over
+    cudaGraphUpload(cg.exec, ls);   // stream-ordered; the first replay then costs what every replay costs
+    if (L.graphs.size() >= 32) {   // a caller cycling through many chunk shapes: start over
         for (auto& g : L.graphs) cudaGraphExecDestroy(g.exec);
         L.graphs.clear();
     }
     L.graphs.push_back(cg);
-    RTCE_CUDA(c, cudaGraphLaunch(cg.exec, ls));
+    return RTCE_OK;
+}
+
+// The stream lane `l` chains on when `nl` lanes rotate: its own, or the context's in strict stream order.
+inline cudaStream_t lane_stream(rtce_ctx* c, int l, int nl) { return nl > 1 ? c->lanes[l].st : c->stream; }
+
+// Graphs of a chunk shape on EVERY lane of the rotation, both for a chain that has the device to itself and for
+// chains side by side: the first call that meets a new shape pays for all lanes, no later call instantiates.
+int capture_shape(rtce_ctx* c, int nl, int frames, int slot0) {
+    for (int l = 0; l < nl; l++) {
+        int r;
+        if ((r = capture_graph(c, l, lane_stream(c, l, nl), frames, slot0, 0))) return r;
+        if (nl > 1 && (r = capture_graph(c, l, lane_stream(c, l, nl), frames, slot0, nl))) return r;
+    }
+    return RTCE_OK;
+}
+
+// Trace one chunk on lane `lane`, whose chain runs on stream `ls`: stage its cameras (pinned ring ->
+// the lane's device buffer, stream-ordered), then either issue the launch chain or — strip plan, no
+// counters / diagnostics — replay the CUDA graph captured from it (RTCE_OPT_GRAPH): ~90 launches on
+// up to 8 streams cost one graph launch on the host.
+int trace_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const rtce_push_constants* pcs, int frames, int slot0, int nl, int crowd) {
+    Lane& L = c->lanes[lane];
+    const int ring = (int)(L.cam_seq++ % kCamRing);
+    RTCE_CUDA(c, cudaEventSynchronize(L.ev_cam[ring]));   // the copy that last used this entry is done
+    Cam* cams = L.h_cams + (size_t)ring * kMaxBatch;
+    fill_cams(c, cams, pcs, frames);
+    RTCE_CUDA(c, cudaMemcpyAsync(L.d_cams, cams, sizeof(Cam) * (size_t)frames, cudaMemcpyHostToDevice, ls));
+    RTCE_CUDA(c, cudaEventRecord(L.ev_cam[ring], ls));
+    if (!graphable(c)) return emit_chunk(c, lane, ls, cams, frames, slot0, crowd);
+    drop_stale_graphs(c, L);
+    const ChunkGraph* g = find_graph(L, frames, slot0, crowd);
+    if (!g) {
+        int r = capture_shape(c, nl, frames, slot0);
+        if (r) return r;
+        g = find_graph(L, frames, slot0, crowd);
+        if (!g) return fail(c, RTCE_ERR_STATE, "launch graph missing after capture");
+    }
+    RTCE_CUDA(c, cudaGraphLaunch(g->exec, ls));
+    c->launches += g->launches;
     return RTCE_OK;
 }
 
@@ -395,6 +368,8 @@ int check_ready(rtce_ctx* c, const void* p, int frames) {
     if (!c) return RTCE_ERR_INVALID;
     if (!p || frames < 1) return fail(c, RTCE_ERR_INVALID, "null push constants or frames < 1");
     if (!c->have_scene || !c->have_view) return fail(c, RTCE_ERR_STATE, "set scene and view before tracing");
+    if (c->marcher != 3 && (c->n_spheres < 1 || c->n_spheres > kSmallSceneMax))
+        return fail(c, RTCE_ERR_INVALID, "RTCE_OPT_MARCHER 1 / 2 need 1 <= objCount <= 8 (algorithm 1 reads objs[0])");
     return RTCE_OK;
 }
 
@@ -411,7 +386,29 @@ int active_lanes(const rtce_ctx* c, int want) {
     return (c->count || c->mark_launches || c->dbg_level >= 0) ? 1 : std::min(want, kMaxLanes);
 }
 
-constexpr int kAccumLanes = 4;   // chunks of rtce_trace_accumulate in flight
+// Windows for `nl` lanes, falling back to strict stream order when the device has no room for them.
+int lanes_with_windows(rtce_ctx* c, int nl) {
+    int r = ensure_pyramid(c, nl);
+    if (r == RTCE_ERR_NOMEM && nl > 1) {
+        nl = 1;
+        r = ensure_pyramid(c, 1);
+    }
+    return r ? r : nl;
+}
+
+// How many lanes other than `lane` still have work on the device.
+int busy_lanes(rtce_ctx* c, int nl, int lane) {
+    int n = 0;
+    for (int l = 0; l < nl; l++) {
+        Lane& L = c->lanes[l];
+        if (l != lane && L.ready && L.pending && cudaEventQuery(L.ev_done) == cudaErrorNotReady) n++;
+    }
+    cudaGetLastError();
+    return n;
+}
+
+// Slot of the window in which chunk [f0, f0 + n) of a batch starts: frame k lands in slot k % slots.
+inline int chunk_slot0(const rtce_ctx* c, int f0, int n) { return f0 % c->slots + n <= c->slots ? f0 % c->slots : 0; }
 
 }  // namespace
 
@@ -421,30 +418,31 @@ int rtce_trace_batch(rtce_ctx* c, const rtce_push_constants* pcs, int frames) {
     int r = check_ready(c, pcs, frames);
     if (r) return r;
     DeviceGuard g(c->device);
-    const int nl = active_lanes(c, c->in_flight);
+    int nl = lanes_with_windows(c, active_lanes(c, c->in_flight));
+    if (nl < 0) return nl;
     c->lanes_active = nl;
-    if ((r = ensure_pyramid(c, nl))) return r;
     if ((r = begin_counters(c))) return r;
-    int lane = 0;
+    int lane = 0, crowd = 0;
     cudaStream_t ls = c->stream;
     if (nl > 1) {
         // frames in flight: this batch goes to the next lane (its own window of slots and its own streams) and
         // starts after everything the caller has enqueued so far — not after the batches on the other lanes
         lane = c->next_lane % nl;
         c->next_lane = (lane + 1) % nl;
-        if ((r = lane_init(c, lane))) return r;
         ls = c->lanes[lane].st;
         RTCE_CUDA(c, cudaEventRecord(c->ev_user, c->stream));
         RTCE_CUDA(c, cudaStreamWaitEvent(ls, c->ev_user, 0));
+        if ((r = comm_wait_lane(c, lane, ls))) return r;   // rtce_gather_frames still reading / filling this window
+        // a caller that waits for every batch gets the launch shape of a chain that owns the device (two frame
+        // groups, every CTA slot); batches issued back to back get the shape that leaves room for each other
+        crowd = busy_lanes(c, nl, lane) > 0 ? nl : 0;
     } else if ((r = flush_lanes(c))) {
         return r;
     }
     const int cs = chunk_size(c);
     for (int f0 = 0; f0 < frames; f0 += cs) {
-        // frame k lands in slot k % slots; chunks always start at slot 0 of their window
         const int n = std::min(cs, frames - f0);
-        const int slot0 = f0 % c->slots + n <= c->slots ? f0 % c->slots : 0;
-        if ((r = trace_chunk(c, lane, ls, pcs + f0, n, slot0))) return r;
+        if ((r = trace_chunk(c, lane, ls, pcs + f0, n, chunk_slot0(c, f0, n), nl, crowd))) return r;
     }
     c->last_lane = lane;
     if (nl > 1) {
@@ -469,47 +467,78 @@ int rtce_flush(rtce_ctx* c) {
     return flush_lanes(c);
 }
 
+// Lanes rtce_trace_accumulate rotates `frames` frames over.
+static int accum_lanes(rtce_ctx* c, int frames) {
+    const int cs = chunk_size(c);
+    int nl = active_lanes(c, std::max(c->in_flight, kAccumLanes));
+    return std::max(1, std::min(nl, (frames + cs - 1) / cs));
+}
+
+int rtce_prepare(rtce_ctx* c, int frames, int accumulate) {
+    if (!c || frames < 1) return fail(c, RTCE_ERR_INVALID, "rtce_prepare: frames < 1");
+    if (!c->have_scene || !c->have_view) return fail(c, RTCE_ERR_STATE, "set scene and view before rtce_prepare");
+    DeviceGuard g(c->device);
+    int nl = lanes_with_windows(c, accumulate ? accum_lanes(c, frames) : active_lanes(c, c->in_flight));
+    if (nl < 0) return nl;
+    if (!graphable(c)) return RTCE_OK;
+    const int cs = chunk_size(c);
+    const uint64_t keep = c->launches;
+    for (int f0 = 0; f0 < frames; f0 += cs) {
+        const int n = std::min(cs, frames - f0);
+        int r = capture_shape(c, nl, n, accumulate ? 0 : chunk_slot0(c, f0, n));   // idempotent: repeated shapes cost a lookup
+        if (r) return r;
+    }
+    c->launches = keep;
+    return RTCE_OK;
+}
+
 int rtce_trace_accumulate(rtce_ctx* c, const rtce_push_constants* pcs, int frames) {
     int r = check_ready(c, pcs, frames);
     if (r) return r;
     DeviceGuard g(c->device);
     const int cs = chunk_size(c);
-    int nl = active_lanes(c, std::max(c->in_flight, kAccumLanes));
-    nl = std::max(1, std::min(nl, (frames + cs - 1) / cs));
-    if ((r = ensure_pyramid(c, nl))) {
-        if (r != RTCE_ERR_NOMEM || nl == 1) return r;
-        nl = 1;   // no room for the extra windows: one chunk at a time
-        if ((r = ensure_pyramid(c, 1))) return r;
-    }
+    int nl = lanes_with_windows(c, accum_lanes(c, frames));
+    if (nl < 0) return nl;
     c->lanes_active = nl;
     if ((r = flush_lanes(c))) return r;
     if ((r = begin_counters(c))) return r;
     const int L = c->levels - 1;
     const size_t npx = (size_t)c->lw[L] * (size_t)c->lh[L];
-    if (c->d_accum_floats < npx) {
+    if (c->d_accum_floats != npx) {
         if (c->d_accum) {
             RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
             RTCE_CUDA(c, cudaFree(c->d_accum));
             c->d_accum = nullptr;
+            c->d_accum_floats = 0;
         }
         cudaError_t e = cudaMalloc(&c->d_accum, npx * sizeof(float));
         if (e != cudaSuccess) return fail(c, RTCE_ERR_NOMEM, "cudaMalloc(accum)", e);
         c->d_accum_floats = npx;
-        RTCE_CUDA(c, cudaMemsetAsync(c->d_accum, 0, npx * sizeof(float), c->stream));   // texels outside a set rect stay 0
+        c->accum_rows[0] = 0;
+        c->accum_rows[1] = c->lh[L];   // everything is stale: cleared below
     }
-    // only the rows of the region of interest are accumulated (whole rows: the image is row-major)
+    // only the rows of the region of interest are accumulated (whole rows: the image is row-major); the rows
+    // outside it are defined to be 0: rows an earlier call wrote under another rect are cleared here
     int rc[4];
     host_level_rect(c->levels, L, c->rect, c->lw[L], c->lh[L], rc);
+    if (c->accum_rows[0] < rc[1]) {
+        const int y1 = std::min(c->accum_rows[1], rc[1]);
+        if (y1 > c->accum_rows[0])
+            RTCE_CUDA(c, cudaMemsetAsync(c->d_accum + (size_t)c->accum_rows[0] * c->lw[L], 0, (size_t)(y1 - c->accum_rows[0]) * c->lw[L] * sizeof(float), c->stream));
+    }
+    if (c->accum_rows[1] > rc[3]) {
+        const int y0 = std::max(c->accum_rows[0], rc[3]);
+        if (c->accum_rows[1] > y0)
+            RTCE_CUDA(c, cudaMemsetAsync(c->d_accum + (size_t)y0 * c->lw[L], 0, (size_t)(c->accum_rows[1] - y0) * c->lw[L] * sizeof(float), c->stream));
+    }
+    c->accum_rows[0] = rc[1];
+    c->accum_rows[1] = rc[3];
     const size_t roi_off = (size_t)rc[1] * (size_t)c->lw[L];
     const size_t roi_n = (size_t)(rc[3] - rc[1]) * (size_t)c->lw[L];
     // The chunks rotate over `nl` lanes (own streams, own window of slots): up to nl chunks are traced side by
     // side — one lane's latency-bound coarse levels under another's final level — while the accumulation runs
     // on the context's stream, chunk after chunk, in frame order.
-    if (nl > 1) {
-        for (int l = 0; l < nl; l++)
-            if ((r = lane_init(c, l))) return r;
-        RTCE_CUDA(c, cudaEventRecord(c->ev_user, c->stream));
-    }
+    if (nl > 1) RTCE_CUDA(c, cudaEventRecord(c->ev_user, c->stream));
     bool first = true;
     int j = 0, lane = 0;
     for (int f0 = 0; f0 < frames; f0 += cs, j++) {
@@ -518,7 +547,7 @@ int rtce_trace_accumulate(rtce_ctx* c, const rtce_push_constants* pcs, int frame
         Lane& W = c->lanes[lane];
         cudaStream_t ls = nl > 1 ? W.st : c->stream;
         if (nl > 1) RTCE_CUDA(c, cudaStreamWaitEvent(ls, j < nl ? c->ev_user : W.ev_free, 0));   // window free again
-        if ((r = trace_chunk(c, lane, ls, pcs + f0, n, 0))) return r;
+        if ((r = trace_chunk(c, lane, ls, pcs + f0, n, 0, nl, nl > 1 ? nl : 0))) return r;
         if (nl > 1) {
             RTCE_CUDA(c, cudaEventRecord(W.ev_done, ls));
             RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, W.ev_done, 0));
@@ -597,7 +626,7 @@ static int ensure_color(rtce_ctx* c) {
     c->d_color = nullptr;
     c->d_rgba8 = nullptr;
     if (cudaMalloc(&c->d_color, px * (size_t)c->slots * sizeof(float4)) != cudaSuccess ||
-        cudaMalloc(&c->d_rgba8, px * sizeof(uchar4)) != cudaSuccess) {
+        cudaMalloc(&c->d_rgba8, px * (size_t)c->slots * sizeof(uchar4)) != cudaSuccess) {
         cudaGetLastError();
         return fail(c, RTCE_ERR_NOMEM, "cudaMalloc(colour slots)");
     }
@@ -614,15 +643,8 @@ static int ensure_color(rtce_ctx* c) {
     return RTCE_OK;
 }
 
-int rtce_shade_batch(rtce_ctx* c, const rtce_push_constants* pcs, int frames) {
-    int r = check_ready(c, pcs, frames);
-    if (r) return r;
-    if (!c->have_materials) return fail(c, RTCE_ERR_STATE, "rtce_shade_batch: materials and lights come with rtce_set_scene");
-    if (frames > c->slots) return fail(c, RTCE_ERR_LIMIT, "rtce_shade_batch: more frames than frame slots");
-    if (!c->d_pyr) return fail(c, RTCE_ERR_STATE, "rtce_shade_batch: nothing traced yet");
-    DeviceGuard g(c->device);
-    if ((r = flush_lanes(c))) return r;
-    if ((r = ensure_color(c))) return r;
+// Shade the final level of slots [slot0, slot0 + frames) of window c->last_lane into the same colour slots.
+static int shade_slots(rtce_ctx* c, const rtce_push_constants* pcs, int frames, int slot0) {
     const int L = c->levels - 1;
     ShadeParams S{};
     S.depth_stride = c->slot_stride;
@@ -657,20 +679,32 @@ int rtce_shade_batch(rtce_ctx* c, const rtce_push_constants* pcs, int frames) {
         S.lpos[i] = make_float4(l[0], l[1], l[2], 0.0f);
         S.lcol[i] = make_float4(l[4], l[5], l[6], 0.0f);
     }
-    if (c->count) RTCE_CUDA(c, cudaMemsetAsync(c->d_shade_counters, 0, 4 * sizeof(unsigned long long), c->stream));
     for (int f0 = 0; f0 < frames; f0 += kMaxBatch) {
         const int n = std::min(kMaxBatch, frames - f0);
         RTCE_CUDA(c, cudaEventSynchronize(c->ev_shade_cams));   // the previous upload has left the staging buffer
         fill_cams(c, c->h_shade_cams, pcs + f0, n);
         RTCE_CUDA(c, cudaMemcpyAsync(c->d_shade_cams, c->h_shade_cams, sizeof(Cam) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
         RTCE_CUDA(c, cudaEventRecord(c->ev_shade_cams, c->stream));
-        S.depth = window_slot(c, c->last_lane, f0) + c->loff[L];
-        S.out = c->d_color + (size_t)f0 * c->d_color_px;
+        S.depth = window_slot(c, c->last_lane, slot0 + f0) + c->loff[L];
+        S.out = c->d_color + (size_t)(slot0 + f0) * c->d_color_px;
         cudaError_t e = launch_shade(S, n, c->count, c->stream);
         if (e != cudaSuccess) return fail(c, RTCE_ERR_CUDA, "shading kernel launch", e);
         c->launches++;
     }
     return RTCE_OK;
+}
+
+int rtce_shade_batch(rtce_ctx* c, const rtce_push_constants* pcs, int frames) {
+    int r = check_ready(c, pcs, frames);
+    if (r) return r;
+    if (!c->have_materials) return fail(c, RTCE_ERR_STATE, "rtce_shade_batch: materials and lights come with rtce_set_scene");
+    if (frames > c->slots) return fail(c, RTCE_ERR_LIMIT, "rtce_shade_batch: more frames than frame slots");
+    if (!c->d_pyr) return fail(c, RTCE_ERR_STATE, "rtce_shade_batch: nothing traced yet");
+    DeviceGuard g(c->device);
+    if ((r = flush_lanes(c))) return r;
+    if ((r = ensure_color(c))) return r;
+    if (c->count) RTCE_CUDA(c, cudaMemsetAsync(c->d_shade_counters, 0, 4 * sizeof(unsigned long long), c->stream));
+    return shade_slots(c, pcs, frames, 0);
 }
 
 int rtce_color_info(const rtce_ctx* c, int slot, int* w, int* h, float** dptr) {
@@ -700,9 +734,11 @@ int rtce_readback_color_rgba8(rtce_ctx* c, int slot, unsigned char* host_rgba8) 
     int r = rtce_color_info(c, slot, nullptr, nullptr, &d);
     if (r) return fail(c, r, "rtce_readback_color_rgba8: nothing shaded or bad slot");
     DeviceGuard g(c->device);
-    cudaError_t e = launch_rgba8(reinterpret_cast<const float4*>(d), c->d_rgba8, c->d_color_px, c->stream);
+    uchar4* d8 = c->d_rgba8 + (size_t)slot * c->d_color_px;
+    cudaError_t e = launch_rgba8(reinterpret_cast<const float4*>(d), d8, c->d_color_px, c->stream);
     if (e != cudaSuccess) return fail(c, RTCE_ERR_CUDA, "rgba8 kernel launch", e);
-    RTCE_CUDA(c, cudaMemcpyAsync(host_rgba8, c->d_rgba8, c->d_color_px * sizeof(uchar4), cudaMemcpyDeviceToHost, c->stream));
+    c->launches++;
+    RTCE_CUDA(c, cudaMemcpyAsync(host_rgba8, d8, c->d_color_px * sizeof(uchar4), cudaMemcpyDeviceToHost, c->stream));
     RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
     return RTCE_OK;
 }
@@ -750,7 +786,7 @@ int rtce_render_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames,
         const int n = std::min(half, frames - f0);
         const int slot0 = pingpong ? phase * half : 0;
         if (used[phase]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));   // half is free again
-        if ((r = trace_chunk(c, 0, c->stream, pcs + f0, n, slot0))) return r;
+        if ((r = trace_chunk(c, 0, c->stream, pcs + f0, n, slot0, 1, 0))) return r;
         RTCE_CUDA(c, cudaEventRecord(c->ev_traced[phase], c->stream));
         RTCE_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_traced[phase], 0));
         for (int k = 0; k < n; k++) {
@@ -759,6 +795,49 @@ int rtce_render_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames,
             RTCE_CUDA(c, cudaMemcpyAsync(dst, src, (size_t)(rc[3] - rc[1]) * w * sizeof(float), cudaMemcpyDeviceToHost,
                                          c->copy_stream));
         }
+        RTCE_CUDA(c, cudaEventRecord(c->ev_copied[phase], c->copy_stream));
+        used[phase] = true;
+        if (!pingpong) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));
+    }
+    RTCE_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+    RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+    return RTCE_OK;
+}
+
+// main.rs:886-914 headless: compute half (trace), render-pass half (shade), "present" (RGBA8 UNORM to host memory).
+// Chunks of min(slots, kMaxBatch) frames on the context's stream; the D2H copy of a chunk's RGBA8 images runs on the
+// copy stream under the tracing of the next chunk (the RGBA8 staging holds one image per slot: two chunks of
+// half the window alternate, as in rtce_render_to_host).
+int rtce_render_rgba8_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames, unsigned char* host_rgba8) {
+    int r = check_ready(c, pcs, frames);
+    if (r) return r;
+    if (!host_rgba8) return fail(c, RTCE_ERR_INVALID, "rtce_render_rgba8_to_host: null output");
+    if (!c->have_materials) return fail(c, RTCE_ERR_STATE, "rtce_render_rgba8_to_host: materials and lights come with rtce_set_scene");
+    DeviceGuard g(c->device);
+    if ((r = ensure_pyramid(c))) return r;
+    if ((r = flush_lanes(c))) return r;
+    if ((r = ensure_color(c))) return r;
+    const int half = std::max(1, std::min(c->slots / 2, kMaxBatch));
+    const bool pingpong = c->slots >= 2;
+    const size_t img_bytes = c->d_color_px * sizeof(uchar4);
+    int phase = 0;
+    bool used[2] = {false, false};
+    for (int f0 = 0; f0 < frames; f0 += half, phase ^= 1) {
+        const int n = std::min(half, frames - f0);
+        const int slot0 = pingpong ? phase * half : 0;
+        if (used[phase]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));   // half is free again
+        c->last_lane = 0;
+        c->lanes_active = 1;
+        if ((r = trace_chunk(c, 0, c->stream, pcs + f0, n, slot0, 1, 0))) return r;
+        if ((r = shade_slots(c, pcs + f0, n, slot0))) return r;
+        cudaError_t e = launch_rgba8(c->d_color + (size_t)slot0 * c->d_color_px, c->d_rgba8 + (size_t)slot0 * c->d_color_px,
+                                     c->d_color_px * (size_t)n, c->stream);
+        if (e != cudaSuccess) return fail(c, RTCE_ERR_CUDA, "rgba8 kernel launch", e);
+        c->launches++;
+        RTCE_CUDA(c, cudaEventRecord(c->ev_traced[phase], c->stream));
+        RTCE_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_traced[phase], 0));
+        RTCE_CUDA(c, cudaMemcpyAsync(host_rgba8 + (size_t)f0 * img_bytes, c->d_rgba8 + (size_t)slot0 * c->d_color_px, img_bytes * (size_t)n,
+                                     cudaMemcpyDeviceToHost, c->copy_stream));
         RTCE_CUDA(c, cudaEventRecord(c->ev_copied[phase], c->copy_stream));
         used[phase] = true;
         if (!pingpong) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));

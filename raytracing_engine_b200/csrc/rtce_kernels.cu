@@ -135,7 +135,7 @@ cudaError_t launch_trace_level_small(const LevelParams& p, int frames, bool coun
 // ------------------------------------------------------------------------------------------
 // Coarse levels (a few thousand rays per frame, but up to ~40 dependent march trips per ray): one
 // thread per pixel, 8x4 pixels per warp, marched to the end in place with the branch-free trip
-// (march_step_pred) — these launches are bound by the latency of the longest ray, not by issue.
+// (march_block) — these launches are bound by the latency of the longest ray, not by issue.
 // Requires RENDER_DIST > 0.
 // ------------------------------------------------------------------------------------------
 template <int N, bool COUNT>
@@ -165,10 +165,9 @@ __global__ void __launch_bounds__(256)
             const float4 row = row_terms(cam, norm_coord(y, P.isy, P.raty));
             Ray<N> ray;
             ray_setup<N>(ray, col, row, start, cam, P.sph);
-            len = 0.0f;
-            bool go = first_step<N, COUNT>(ray, len, P.threshold, P.render_dist, cE, cS);
+            bool go = first_trip<N, COUNT>(ray, len, P.threshold, P.render_dist, cE, cS);
             float last = len;
-            while (go) go = march_block_pred<N, COUNT, RTCE_PRED_BLOCK>(ray, len, last, P.threshold, P.render_dist, P.sph, cE, cS);
+            while (go) go = march_block<N, COUNT, RTCE_PRED_BLOCK>(ray, len, last, P.threshold, P.render_dist, P.sph, cE, cS);
         }
         P.out[(size_t)f * P.slot_stride + (size_t)y * (size_t)P.w + (size_t)x] = glsl_max(fadd(start, len), 0.0f);   // :84, :86
         cR = 1;

@@ -5,6 +5,26 @@
 
 namespace rtce {
 
+// Per-device launch configuration is cached per DEVICE (a process may hold contexts on several GPUs): index = CUDA
+// device ordinal.  Entries are written once with values that depend only on (kernel, device), so a race between two
+// host threads writes the same values twice.
+constexpr int kMaxDevices = 64;
+inline int current_device_slot() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return dev >= 0 && dev < kMaxDevices ? dev : 0;
+}
+inline int device_sm_count() {
+    static int sms[kMaxDevices] = {};
+    const int d = current_device_slot();
+    if (!sms[d]) {
+        int n = 148;
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, d);
+        sms[d] = n > 0 ? n : 148;
+    }
+    return sms[d];
+}
+
 constexpr int kMaxBatch = 32;        // frames per launch (camera table lives in kernel params)
 constexpr int kSmallSceneMax = 8;    // MAX_OBJECTS of the reference shader (utilities.glsl:3)
 constexpr int kMaxLevels = 16;
@@ -45,7 +65,7 @@ cudaError_t launch_trace_level_small(const LevelParams& p, int frames, bool coun
 // short correctly rounded sqrt.  Requires RENDER_DIST > 0.
 cudaError_t launch_trace_level_pix(const LevelParams& p, int frames, bool count, cudaStream_t st);
 
-// Large scenes (objCount > 8): spheres in global memory, one CTA per ray.
+// Large scenes (objCount > 8, extension of utilities.glsl:3): spheres in global memory.
 struct LevelParamsLarge {
     float* out;
     const float* parent;
@@ -59,54 +79,9 @@ struct LevelParamsLarge {
     float isx, isy, ratx, raty, threshold, render_dist;
     Cam cam[kMaxBatch];
 };
-cudaError_t launch_trace_level_large(const LevelParamsLarge& p, int frames, bool count, cudaStream_t st);
-// Same contract, the per-ray cache of lower bounds in registers (rtce_kernels_large_reg.cu); n_spheres <= large_reg_capacity().
+// The per-ray cache of lower bounds in registers (rtce_kernels_large_reg.cu); n_spheres <= large_reg_capacity().
 cudaError_t launch_trace_level_large_reg(const LevelParamsLarge& p, int frames, bool count, cudaStream_t st);
 int large_reg_capacity();
-
-// ---- fused pyramid kernel (objCount <= 8): ALL levels of a frame batch in ONE launch ---------
-// One CTA owns one 64x64 tile of the final level and, before it, the tile's ancestor regions on
-// every coarser level (32x32, 16x16, ... 1 pixel), handing each level to the next through shared
-// memory.  Legal because a pixel's value is a pure function of (x, y, level, uniforms): ancestors
-// shared by several tiles are recomputed per tile with identical bits.
-constexpr int kFusedTile = 64;
-constexpr int kFusedThreads = 256;
-constexpr int kFusedMaxSide = 72;      // largest region side at any level (table size)
-constexpr int kFusedOddPitch = 44;     // parent buffer of shift 1, 3, 5, ... (region side <= 44)
-constexpr int kFusedEvenPitch = 28;    // parent buffer of shift 2, 4, 6, ... (region side <= 28)
-
-struct FusedLevel {
-    unsigned long long off;   // float offset of the level image inside a frame slot
-    float isx, isy;           // pc.imageSize at this level (main.rs:303-305)
-    float threshold;          // compute.glsl:75
-    int w, h;                 // level image size (pitch = w)
-    int rx0, ry0, rx1, ry1;   // region of interest at this level (whole level, or a rect's ancestors)
-};
-
-struct FusedParams {
-    float* base;              // frame slot 0 of the pyramid
-    size_t slot_stride;
-    unsigned long long* counters;
-    int levels, n_spheres;
-    int gx0, gy0;             // final-level origin of the tile grid (multiple of kFusedTile)
-    int ntx, nty;
-    float ratx, raty, render_dist;
-    FusedLevel lv[kMaxLevels];
-    float4 sph[kSmallSceneMax];
-    const Cam* cams;          // the cameras in device memory (cluster kernel; the fused kernel reads cam[])
-    Cam cam[kMaxBatch];
-};
-// Returns cudaErrorNotSupported when the geometry does not fit the kernel's shared-memory regions
-// (the caller then uses the per-level kernels).
-bool fused_geometry_ok(const FusedParams& p);
-cudaError_t launch_trace_fused(const FusedParams& p, int frames, bool count, cudaStream_t st);
-
-// ---- cluster kernel (objCount <= 8): the coarse levels [0, p.levels) of a frame batch in ONE launch ----
-// One thread-block cluster (1..8 CTAs of kCoarseThreads) per frame walks the levels with a cluster
-// barrier in between; FusedParams describes the level prefix (fill as for the fused kernel, plus
-// `cams`; gx0 / gy0 / ntx / nty and cam[] are not used).  Requires RENDER_DIST > 0.
-constexpr int kCoarseThreads = 512;
-cudaError_t launch_trace_coarse(const FusedParams& p, int frames, bool count, cudaStream_t st);
 
 // ---- strip kernel (objCount <= 8): ONE level of a frame batch, persistent warps ---------------
 // The levels that hold almost all rays (the last three: 75 % + 19 % + 5 %) are each traced by one

@@ -12,7 +12,7 @@
 // Divergence (measured on the default scene, all levels >= 2: 77 % of rays end in the first march
 // trip, 20 % in the second, 3 % form a long tail of up to ~30 trips; hit pixels are spatially
 // coherent, the tail is not):
-//   trip 1  is straight-line code for all 32 lanes (no SDF evaluation: see first_step);
+//   trip 1  is straight-line code for all 32 lanes (no SDF evaluation: see first_trip);
 //   trip 2  runs in place, under one warp-uniform branch (taken by the ~23 % of warps that cover
 //           hit pixels, where nearly all lanes take it);
 //   trips 3.. are rare per warp, so those rays are compacted: ballot + prefix-popcount push into a
@@ -163,7 +163,7 @@ RTCE_DEV int tail_march(float* q, int qn, const bool drain, float* __restrict__ 
         }
         if (active) {
             unsigned e = 0, s = 0;
-            const bool go = march_step<N, COUNT>(r, len, last, thr, rd, sph, e, s);
+            const bool go = march_trip<N, COUNT, false>(r, len, last, thr, rd, sph, e, s);
             if (COUNT) { cE += e; cS += s; }
             age++;
             if (!go) {
@@ -226,9 +226,9 @@ __global__ void __launch_bounds__(128)
         if (active) {
             unsigned e = 0, s = 0;
 #if RTCE_OQ_BRANCHY
-            const bool go = march_step<N, COUNT>(r, len, last, thr, rd, sph, e, s);
+            const bool go = march_trip<N, COUNT, false>(r, len, last, thr, rd, sph, e, s);
 #else
-            const bool go = march_block_pred<N, COUNT, RTCE_PRED_BLOCK>(r, len, last, thr, rd, sph, e, s);
+            const bool go = march_block<N, COUNT, RTCE_PRED_BLOCK>(r, len, last, thr, rd, sph, e, s);
 #endif
             if (COUNT) { cE += e; cS += s; }
             if (!go) {
@@ -247,25 +247,6 @@ __global__ void __launch_bounds__(128)
             atomicAdd(P.counters + 2, (unsigned long long)cS);
         }
     }
-}
-
-// First trip of the march loop for RENDER_DIST > 0, branch-free (see first_step in rtce_march.cuh).
-template <int N, bool COUNT>
-RTCE_DEV bool first_trip(const Ray<N>& r, float& len, const float thr, const float rd, unsigned& cE, unsigned& cS) {
-    float dist = rd;   // compute.glsl:49
-#pragma unroll
-    for (int i = 0; i < N; i++) {
-        if (COUNT) cE += (r.d[i] <= thr) ? 1u : 0u;
-        dist = glsl_min(dist, r.d[i]);
-    }
-    if (COUNT) {
-        cE += N;
-        cS++;
-    }
-    const float last = glsl_max(dist, 0.0f);   // :59; len = 0 + last
-    const bool hit = dist <= thr;              // :62 (radius = (0 + 1) * threshold)
-    len = hit ? fsub(last, thr) : last;        // :63
-    return !hit && last < rd;                  // :44
 }
 
 RTCE_DEV unsigned long long globaltimer_ns() {
@@ -428,7 +409,7 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
                 float last = len;   // len = 0 + last after the first trip
                 if (cont) {
                     e = 0, s = 0;
-                    cont2 = march_step<N, COUNT>(ray, len, last, thr, rd, sph, e, s);
+                    cont2 = march_trip<N, COUNT, false>(ray, len, last, thr, rd, sph, e, s);
                     if (COUNT) { cE += e; cS += s; }
                     if (!cont2) *op = glsl_max(fadd(start, len), 0.0f);
                 }
@@ -476,23 +457,21 @@ __global__ void __launch_bounds__(kStripThreads, RTCE_STRIP_MIN_BLOCKS)
 template <int N, bool COUNT, bool HAS_PARENT>
 static cudaError_t launch_strip_ncp(const StripParams& p, cudaStream_t st) {
     const int smem = (kStripThreads / 32) * (RTCE_SQ_WORDS(N) * kQCap + 4 * kStripMaxRows + kPinWords) * (int)sizeof(float);
-    static bool configured = false;   // per instantiation
-    static int resident = 148 * 3;    // CTAs the device holds at once
-    static int n_sms = 148;
-    if (!configured) {
+    // per instantiation AND per device: function attributes and occupancy belong to the device's copy of the kernel
+    static int resident_of[kMaxDevices] = {};   // CTAs the device holds at once; 0 = not configured yet
+    const int dslot = current_device_slot();
+    const int n_sms = device_sm_count();
+    if (!resident_of[dslot]) {
         cudaError_t e = cudaFuncSetAttribute(k_trace_strip<N, COUNT, HAS_PARENT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(k_trace_strip<N, COUNT, HAS_PARENT>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
         if (e != cudaSuccess) return e;
-        int dev = 0, sms = 148, per_sm = 3;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        int per_sm = 3;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_strip<N, COUNT, HAS_PARENT>, kStripThreads, smem);
         if (e != cudaSuccess) return e;
-        resident = sms * (per_sm > 0 ? per_sm : 1);
-        n_sms = sms;
-        configured = true;
+        resident_of[dslot] = n_sms * (per_sm > 0 ? per_sm : 1);
     }
+    const int resident = resident_of[dslot];
     // persistent CTAs: one resident wave for the whole batch
     const long long tasks = (long long)p.ntx * p.nty * p.frames;
     long long ctas = resident / (p.cta_share > 1 ? p.cta_share : 1);
@@ -535,14 +514,8 @@ cudaError_t launch_trace_strip(const StripParams& p, bool count, cudaStream_t st
 
 template <int N>
 static cudaError_t launch_overflow_n(const OverflowParams& p, bool count, cudaStream_t st) {
-    static int ctas = 0;
-    if (!ctas) {
-        int dev = 0, sms = 148;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        ctas = sms * 2;   // up to two warps per scheduler (see the kernel); a 128-thread CTA fits beside three
-                          // resident strip CTAs
-    }
+    const int ctas = device_sm_count() * 2;   // up to two warps per scheduler (see the kernel); a 128-thread CTA fits
+                                              // beside three resident strip CTAs
     if (count)
         k_march_overflow<N, true><<<ctas, 128, 0, st>>>(p);
     else

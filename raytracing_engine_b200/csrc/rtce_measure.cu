@@ -124,3 +124,41 @@ extern "C" int rtce_selftest_math(int device, uint64_t out4[4]) {
     cudaSetDevice(prev);
     return rc;
 }
+
+// ------------------------------------------------------------------------------------------------
+// rtce_selftest_repeat — utilities.glsl:32-34 `repeat` (unused by the reference's shaders) on the device.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+__global__ void __launch_bounds__(256) k_selftest_repeat(const float* __restrict__ p, const float* __restrict__ r,
+                                                         float* __restrict__ out, size_t n) {
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) out[i] = rtce::repeat1(p[i], r[i]);
+}
+
+}  // namespace
+
+extern "C" int rtce_selftest_repeat(int device, const float* p, const float* r, float* out, size_t n) {
+    if (!p || !r || !out) return RTCE_ERR_INVALID;
+    if (!n) return RTCE_OK;
+    int prev = 0;
+    if (cudaGetDevice(&prev) != cudaSuccess) return RTCE_ERR_CUDA;
+    if (cudaSetDevice(device) != cudaSuccess) return RTCE_ERR_CUDA;
+    float *dp = nullptr, *dr = nullptr, *dout = nullptr;
+    int rc = RTCE_OK;
+    const size_t bytes = n * sizeof(float);
+    if (cudaMalloc(&dp, bytes) != cudaSuccess || cudaMalloc(&dr, bytes) != cudaSuccess || cudaMalloc(&dout, bytes) != cudaSuccess) {
+        rc = RTCE_ERR_NOMEM;
+    } else if (cudaMemcpy(dp, p, bytes, cudaMemcpyHostToDevice) != cudaSuccess || cudaMemcpy(dr, r, bytes, cudaMemcpyHostToDevice) != cudaSuccess) {
+        rc = RTCE_ERR_CUDA;
+    } else {
+        k_selftest_repeat<<<148 * 4, 256>>>(dp, dr, dout, n);
+        if (cudaMemcpy(out, dout, bytes, cudaMemcpyDeviceToHost) != cudaSuccess) rc = RTCE_ERR_CUDA;
+    }
+    cudaGetLastError();
+    cudaFree(dp);
+    cudaFree(dr);
+    cudaFree(dout);
+    cudaSetDevice(prev);
+    return rc;
+}

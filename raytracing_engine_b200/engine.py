@@ -16,13 +16,17 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "librtce.so")
 
 RTCE_OK = 0
-OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS, OPT_COARSE_FUSED, OPT_STRIP_ROWS = 1, 2, 3, 4, 5, 6, 7
+OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS, OPT_STRIP_ROWS = 1, 2, 3, 4, 5, 7
 OPT_GRAPH = 8
 OPT_FRAMES_IN_FLIGHT = 9
 OPT_STRIP_CTAS_PER_SM = 10
 OPT_FAR_MISS = 11
 OPT_LARGE_KERNEL = 12
-KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_FUSED, KERNEL_STRIP = 0, 1, 2, 3
+OPT_MARCHER = 13
+KERNEL_AUTO, KERNEL_PER_LEVEL, KERNEL_STRIP = 0, 1, 3
+LARGE_AUTO, LARGE_REGISTER, LARGE_EVENT = 0, 2, 3
+ABI_VERSION = 2
+COMM_ID_BYTES = 128
 
 # compute.glsl:7-12 PushConstantData, 40 bytes
 PUSH_CONSTANTS_DTYPE = np.dtype(
@@ -35,12 +39,15 @@ EXPORTS = [
     "rtce_set_option", "rtce_set_stream", "rtce_set_scene", "rtce_set_spheres", "rtce_set_view",
     "rtce_set_rect", "rtce_level_count", "rtce_level_info", "rtce_host_level_count",
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
-    "rtce_trace_accumulate", "rtce_accum_info", "rtce_readback", "rtce_readback_accum",
-    "rtce_render_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_flush", "rtce_get_counters",
+    "rtce_trace_accumulate", "rtce_accum_info", "rtce_prepare", "rtce_readback", "rtce_readback_accum",
+    "rtce_render_to_host", "rtce_render_rgba8_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_flush", "rtce_get_counters",
     "rtce_get_level_counters", "rtce_get_far_miss_rays",
     "rtce_shade_batch", "rtce_color_info", "rtce_readback_color", "rtce_readback_color_rgba8", "rtce_get_shade_counters",
-    "rtce_measure_fp32_issue", "rtce_selftest_math", "rtce_debug_strip_timeline",
+    "rtce_measure_fp32_issue", "rtce_selftest_math", "rtce_selftest_repeat", "rtce_debug_strip_timeline",
     "rtce_debug_launch_timeline",
+    "rtce_camera_rotation", "rtce_camera_pose",
+    "rtce_comm_unique_id", "rtce_comm_init", "rtce_host_band_rows", "rtce_gather_accum", "rtce_gather_frames", "rtce_gather_wait",
+    "rtce_gather_info", "rtce_readback_gathered", "rtce_gather_last_ms",
 ]
 
 
@@ -90,6 +97,20 @@ def load_library() -> C.CDLL:
         "rtce_readback": (i32, [vp, i32, i32, vp, sz]),
         "rtce_readback_accum": (i32, [vp, vp, sz]),
         "rtce_render_to_host": (i32, [vp, vp, i32, vp]),
+        "rtce_render_rgba8_to_host": (i32, [vp, vp, i32, vp]),
+        "rtce_prepare": (i32, [vp, i32, i32]),
+        "rtce_selftest_repeat": (i32, [i32, vp, vp, vp, sz]),
+        "rtce_camera_rotation": (i32, [f32, f32, vp]),
+        "rtce_camera_pose": (i32, [f32, f32, vp, vp]),
+        "rtce_comm_unique_id": (i32, [vp]),
+        "rtce_comm_init": (i32, [vp, vp, i32, i32]),
+        "rtce_host_band_rows": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
+        "rtce_gather_accum": (i32, [vp, i32, vp]),
+        "rtce_gather_frames": (i32, [vp, i32, vp, i32]),
+        "rtce_gather_wait": (i32, [vp]),
+        "rtce_gather_info": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(vp)]),
+        "rtce_readback_gathered": (i32, [vp, vp, sz]),
+        "rtce_gather_last_ms": (i32, [vp, C.POINTER(f32)]),
         "rtce_host_alloc": (i32, [C.POINTER(vp), sz]),
         "rtce_host_free": (i32, [vp]),
         "rtce_sync": (i32, [vp]),
@@ -159,6 +180,56 @@ def selftest_math(device: int = 0) -> dict:
         raise RtceError(f"rtce_selftest_math: {r}")
     return {"sqrt_mismatches": int(out[0]), "rcp_mismatches": int(out[1]),
             "sqrt_checked": int(out[2]), "rcp_checked": int(out[3])}
+
+
+def selftest_repeat(p, r, device: int = 0) -> np.ndarray:
+    """utilities.glsl:32-34 `repeat` evaluated on the GPU, componentwise."""
+    p = np.ascontiguousarray(p, dtype=np.float32).ravel()
+    r = np.ascontiguousarray(r, dtype=np.float32).ravel()
+    assert p.size == r.size
+    out = np.empty_like(p)
+    rc = load_library().rtce_selftest_repeat(int(device), p.ctypes.data, r.ctypes.data, out.ctypes.data, p.size)
+    if rc != RTCE_OK:
+        raise RtceError(f"rtce_selftest_repeat: {rc}")
+    return out
+
+
+def camera_rotation(yaw: float, pitch: float) -> np.ndarray:
+    """main.rs:402-404 in binary32 (rtce_camera_rotation): [x, y, z, w]."""
+    q = np.zeros(4, dtype=np.float32)
+    rc = load_library().rtce_camera_rotation(float(yaw), float(pitch), q.ctypes.data)
+    if rc != RTCE_OK:
+        raise RtceError(f"rtce_camera_rotation: {rc}")
+    return q
+
+
+def camera_pose(yaw: float, pitch: float, local_delta, pc: np.ndarray) -> np.ndarray:
+    """main.rs:770-773 (rtce_camera_pose): clamps the pitch, writes pc['rot'], adds the rotated local delta to pc['pos'].
+    `pc` is ONE PushConstantData record (0-d or length-1 array of PUSH_CONSTANTS_DTYPE), updated in place."""
+    assert pc.dtype == PUSH_CONSTANTS_DTYPE and pc.size == 1 and pc.flags["C_CONTIGUOUS"]
+    d = None if local_delta is None else np.ascontiguousarray(local_delta, dtype=np.float32)
+    rc = load_library().rtce_camera_pose(float(yaw), float(pitch), d.ctypes.data if d is not None else None, pc.ctypes.data)
+    if rc != RTCE_OK:
+        raise RtceError(f"rtce_camera_pose: {rc}")
+    return pc
+
+
+def host_band_rows(height: int, world: int, rank: int):
+    """Equal split of the final level's rows in whole 8-row dispatch rows (rtce_host_band_rows)."""
+    y0, y1 = C.c_int(), C.c_int()
+    rc = load_library().rtce_host_band_rows(int(height), int(world), int(rank), C.byref(y0), C.byref(y1))
+    if rc != RTCE_OK:
+        raise RtceError(f"rtce_host_band_rows: {rc}")
+    return y0.value, y1.value
+
+
+def comm_unique_id() -> bytes:
+    """ncclGetUniqueId through the library (rank 0 calls it and distributes the 128 bytes)."""
+    buf = C.create_string_buffer(COMM_ID_BYTES)
+    rc = load_library().rtce_comm_unique_id(buf)
+    if rc != RTCE_OK:
+        raise RtceError(f"rtce_comm_unique_id: {rc} (libnccl.so.2 not found?)")
+    return buf.raw
 
 
 def make_push_constants(rots, poss) -> np.ndarray:
@@ -281,6 +352,55 @@ class Engine:
         self._check(self.lib.rtce_trace_accumulate(self._ctx, pcs.ctypes.data, pcs.shape[0]),
                     "rtce_trace_accumulate")
 
+    def prepare(self, frames: int, accumulate: bool = False):
+        """Allocate every lane's windows and capture the launch graphs of a batch of `frames` frames now."""
+        self._check(self.lib.rtce_prepare(self._ctx, int(frames), int(bool(accumulate))), "rtce_prepare")
+
+    def accum_info(self):
+        w, h, p = C.c_int(), C.c_int(), C.c_void_p()
+        self._check(self.lib.rtce_accum_info(self._ctx, C.byref(w), C.byref(h), C.byref(p)), "rtce_accum_info")
+        return w.value, h.value, p.value
+
+    # -- several GPUs: the one exchange ---------------------------------------------------------
+    def comm_init(self, unique_id: bytes, rank: int, world: int):
+        assert len(unique_id) == COMM_ID_BYTES
+        self._check(self.lib.rtce_comm_init(self._ctx, unique_id, int(rank), int(world)), "rtce_comm_init")
+
+    def gather_accum(self, dst: int = 0, bands=None):
+        """Gather the accumulated image's row bands to rank `dst` (stream-ordered, overlaps later tracing)."""
+        tab = None
+        if bands is not None:
+            tab = np.ascontiguousarray(np.asarray(bands, dtype=np.int32).reshape(-1, 2))
+        self._check(self.lib.rtce_gather_accum(self._ctx, int(dst), tab.ctypes.data if tab is not None else None),
+                    "rtce_gather_accum")
+
+    def gather_frames(self, dst: int, bands, frames: int):
+        """Gather the final-level row bands of slots 0..frames-1 of the latest batch to rank `dst`, in place."""
+        tab = None
+        if bands is not None:
+            tab = np.ascontiguousarray(np.asarray(bands, dtype=np.int32).reshape(-1, 2))
+        self._check(self.lib.rtce_gather_frames(self._ctx, int(dst), tab.ctypes.data if tab is not None else None, int(frames)),
+                    "rtce_gather_frames")
+
+    def gather_wait(self):
+        self._check(self.lib.rtce_gather_wait(self._ctx), "rtce_gather_wait")
+
+    def gather_info(self):
+        w, h, p = C.c_int(), C.c_int(), C.c_void_p()
+        self._check(self.lib.rtce_gather_info(self._ctx, C.byref(w), C.byref(h), C.byref(p)), "rtce_gather_info")
+        return w.value, h.value, p.value
+
+    def readback_gathered(self) -> np.ndarray:
+        w, h, _ = self.level_info(-1, 0)
+        out = np.empty((h, w), dtype=np.float32)
+        self._check(self.lib.rtce_readback_gathered(self._ctx, out.ctypes.data, 0), "rtce_readback_gathered")
+        return out
+
+    def gather_last_ms(self) -> float:
+        ms = C.c_float()
+        self._check(self.lib.rtce_gather_last_ms(self._ctx, C.byref(ms)), "rtce_gather_last_ms")
+        return float(ms.value)
+
     def sync(self):
         self._check(self.lib.rtce_sync(self._ctx), "rtce_sync")
 
@@ -340,6 +460,17 @@ class Engine:
         assert out.dtype == np.float32 and out.size == pcs.shape[0] * h * w and out.flags["C_CONTIGUOUS"]
         self._check(self.lib.rtce_render_to_host(self._ctx, pcs.ctypes.data, pcs.shape[0], out.ctypes.data),
                     "rtce_render_to_host")
+        return out
+
+    def render_rgba8_to_host(self, pcs: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """Headless frame loop body (main.rs:886-914): trace + shade + RGBA8 UNORM images to host memory."""
+        pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
+        vw, vh = int(self.view[0]), int(self.view[1])
+        if out is None:
+            out = np.empty((pcs.shape[0], vh, vw, 4), dtype=np.uint8)
+        assert out.dtype == np.uint8 and out.size == pcs.shape[0] * vh * vw * 4 and out.flags["C_CONTIGUOUS"]
+        self._check(self.lib.rtce_render_rgba8_to_host(self._ctx, pcs.ctypes.data, pcs.shape[0], out.ctypes.data),
+                    "rtce_render_rgba8_to_host")
         return out
 
     def strip_timeline(self, level: int = -1, max_warps: int = 8192, fetch: bool = True):

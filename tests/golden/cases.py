@@ -39,6 +39,9 @@ def cases():
     c.append(("empty_scene_160x96", "ref", np.zeros((0, 4), np.float32), 160, 96, 0, ident, zero, True))
     c.append(("one_sphere_160x96", "ref", DEFAULT[:1], 160, 96, 0, rots[7], poss[7], True))
     c.append(("eight_spheres_320x200", "ref", _rng_spheres(8, 1), 320, 200, 0, rots[9], poss[9], False))
+    # MAX_OBJECTS = 8 (utilities.glsl:3) at BASELINE's 1080p: the default four spheres plus four more
+    c.append(("eight_spheres_1080p", "ref", np.concatenate([DEFAULT, _rng_spheres(4, 11, box=9.0, rmax=2.5)]), 1920, 1080, 0,
+              rots[6], poss[6], False))
     # camera inside a sphere (negative SDF at the origin) and looking away (mostly misses)
     c.append(("inside_sphere_200x120", "ref", np.array([[0, 0.5, 0, 3.0], [4, 9, 1, 2.0]], np.float32), 200, 120, 0,
               ident, zero, True))

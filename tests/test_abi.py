@@ -24,11 +24,11 @@ def _declared():
 def test_library_exports_every_declared_symbol():
     lib = rt.load_library()
     names = _declared()
-    assert len(names) >= 25
+    assert len(names) >= 50
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/rtce.h but not exported by librtce.so"
     assert sorted(engine.EXPORTS) == names
-    assert lib.rtce_abi_version() == 1
+    assert lib.rtce_abi_version() == engine.ABI_VERSION == 2
 
 
 def test_struct_layouts_match_reference():
@@ -113,3 +113,102 @@ def test_rust_binding_source_matches_the_header():
         assert (args.count(",") + 1 if args else 0) == c_fns[name], name
         n += 1
     assert n >= 25
+
+
+def test_header_compiles_as_c11_and_links_against_the_library(tmp_path):
+    """include/rtce.h consumed by a plain C compiler (gcc -std=c11 -pedantic -Wall -Werror), the program linked against
+    librtce.so: the header itself is the contract, not its Python or nvcc mirror.  Without a GPU the program checks the
+    layouts, the host-side entry points and that rtce_create reports the missing device as an error code."""
+    import subprocess
+    src = tmp_path / "consumer.c"
+    src.write_text(r"""
+#include <stddef.h>
+#include <stdio.h>
+#include <string.h>
+#include "rtce.h"
+_Static_assert(sizeof(rtce_push_constants) == 40, "PushConstantData is 40 bytes");
+_Static_assert(offsetof(rtce_push_constants, pos) == 16 && offsetof(rtce_push_constants, iter) == 28 &&
+               offsetof(rtce_push_constants, imageSize) == 32, "push-constant offsets (compute.glsl:7-12)");
+_Static_assert(sizeof(rtce_constant_buffer) == 16 && sizeof(rtce_sphere) == 16, "ConstantBuffer / Object");
+_Static_assert(sizeof(rtce_counters) == 32, "counters");
+int main(void) {
+    if (rtce_abi_version() != RTCE_ABI_VERSION) return 1;
+    if (rtce_host_level_count(1920.0f, 0) != 8 || rtce_host_level_count(800.0f, 1) != 8) return 2;
+    int w = 0, h = 0;
+    if (rtce_host_level_dims(8, 1920.0f, 1080.0f, 7, &w, &h) != RTCE_OK || w != 1920 || h != 1080) return 3;
+    float isz[2];
+    if (rtce_host_image_size(8, 7, 1920.0f, 1080.0f, isz) != RTCE_OK || isz[0] != 1.0f / 1920.0f) return 4;
+    int y0 = 0, y1 = 0;
+    if (rtce_host_band_rows(4320, 8, 7, &y0, &y1) != RTCE_OK || y1 != 4320 || y1 - y0 != 536) return 5;
+    rtce_push_constants pc;
+    memset(&pc, 0, sizeof pc);
+    const float delta[3] = {0.0f, 2.0f, 0.0f};
+    if (rtce_camera_pose(0.0f, 0.0f, delta, &pc) != RTCE_OK) return 6;
+    if (pc.rot[0] != 0.0f || pc.rot[1] != 0.0f || pc.rot[2] != 0.0f || pc.rot[3] != 1.0f) return 7;   /* identity */
+    if (pc.pos[0] != 0.0f || pc.pos[1] != 2.0f || pc.pos[2] != 0.0f) return 8;                         /* forward = +Y */
+    rtce_ctx* ctx = NULL;
+    int r = rtce_create(0, 1000.0f, &ctx);
+    if (r == RTCE_OK) {                      /* a GPU is present: one tiny frame through the header's own types */
+        unsigned char md[RTCE_MUTABLE_DATA_SIZE];
+        memset(md, 0, sizeof md);
+        unsigned n = 1; memcpy(md + RTCE_MUTABLE_DATA_OBJCOUNT_OFFSET, &n, 4);
+        rtce_sphere s = {{0.0f, 6.0f, 0.0f}, 2.0f}; memcpy(md + RTCE_MUTABLE_DATA_OBJS_OFFSET, &s, sizeof s);
+        rtce_constant_buffer cb = {{64.0f, 48.0f}, {1.0f, 48.0f / 64.0f}};
+        static float img[64 * 48];
+        if (rtce_set_scene(ctx, md, sizeof md) || rtce_set_view(ctx, &cb, 0) || rtce_trace(ctx, &pc) ||
+            rtce_readback(ctx, -1, 0, img, 0)) { printf("%s\n", rtce_last_error(ctx)); return 9; }
+        if (!(img[24 * 64 + 32] > 1.0f && img[24 * 64 + 32] < 6.0f)) return 10;   /* the centre ray stops on the sphere */
+        rtce_destroy(ctx);
+    } else if (r != RTCE_ERR_CUDA || ctx != NULL) {
+        return 11;
+    }
+    puts("ok");
+    return 0;
+}
+""")
+    exe = tmp_path / "consumer"
+    libdir = os.path.dirname(engine.LIB_PATH)
+    cmd = ["gcc", "-std=c11", "-pedantic", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(ROOT, "include"), str(src),
+           "-o", str(exe), "-L", libdir, "-lrtce", f"-Wl,-rpath,{libdir}"]
+    env = dict(os.environ)
+    env.pop("CC", None)
+    out = subprocess.run(cmd, capture_output=True, text=True, env=env)
+    assert out.returncode == 0, out.stderr
+    run = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert run.returncode == 0 and run.stdout.strip() == "ok", (run.returncode, run.stdout, run.stderr)
+
+
+def test_camera_pose_matches_the_float64_generator_and_is_exact_at_identity():
+    """rtce_camera_rotation / rtce_camera_pose (main.rs:402-414, 770-773 in binary32) against camera.py (float64,
+    rounded once): within 1 ulp-ish (4e-7 relative to the largest component), exact at yaw = pitch = 0, pitch clamped."""
+    from raytracing_engine_b200 import camera
+    assert np.array_equal(rt.camera_rotation(0.0, 0.0), np.array([0, 0, 0, 1], np.float32))
+    rs = np.random.RandomState(5)
+    for _ in range(200):
+        yaw, pitch = float(rs.uniform(-7, 7)), float(rs.uniform(-1.5, 1.5))
+        q = rt.camera_rotation(yaw, pitch)
+        assert np.abs(q.astype(np.float64) - camera.rotation(yaw, pitch).astype(np.float64)).max() <= 2.4e-7
+        assert abs(float(np.sum(q.astype(np.float64) ** 2)) - 1.0) < 1e-6
+        delta = rs.uniform(-30, 30, 3).astype(np.float32)
+        pos0 = rs.uniform(-100, 100, 3).astype(np.float32)
+        pc = rt.make_push_constants([[0, 0, 0, 1]], [pos0])
+        rt.camera_pose(yaw, pitch, delta, pc)
+        assert np.array_equal(pc["rot"][0], q)
+        want = camera.advance(pos0, yaw, pitch, delta)
+        assert np.abs(pc["pos"][0].astype(np.float64) - want.astype(np.float64)).max() <= 4e-5
+        assert pc["iter"][0] == 0 and np.array_equal(pc["imageSize"][0], np.array([1, 1], np.float32))
+    pc = rt.make_push_constants([[0, 0, 0, 1]], [[1, 2, 3]])
+    rt.camera_pose(0.0, 0.0, [0.5, -2.0, 4.0], pc)                 # identity: axes are the world axes, sums exact
+    assert np.array_equal(pc["pos"][0], np.array([1.5, 0.0, 7.0], np.float32))
+    a = rt.make_push_constants([[0, 0, 0, 1]], [[0, 0, 0]])
+    b = rt.make_push_constants([[0, 0, 0, 1]], [[0, 0, 0]])
+    rt.camera_pose(0.4, 9.0, None, a)                               # main.rs:770 clamp
+    rt.camera_pose(0.4, float(np.float32(0.5) * np.float32(np.pi)), None, b)
+    assert np.array_equal(a["rot"], b["rot"])
+
+
+def test_band_rows_in_c_equal_the_python_partition():
+    from raytracing_engine_b200 import sharding
+    for H in (8, 48, 136, 600, 1080, 2160, 4320):
+        for world in (1, 2, 3, 4, 8):
+            assert [rt.host_band_rows(H, world, r) for r in range(world)] == sharding.all_bands(H, world)
