@@ -84,6 +84,50 @@ extern "C" {
     fn rtce_readback_color_rgba8(ctx: *mut rtce_ctx, slot: c_int, host_rgba8: *mut u8) -> c_int;
     fn rtce_host_alloc(out: *mut *mut c_void, nbytes: usize) -> c_int;
     fn rtce_host_free(p: *mut c_void) -> c_int;
+    fn rtce_prepare(ctx: *mut rtce_ctx, frames: c_int, accumulate: c_int) -> c_int;
+    fn rtce_render_rgba8_to_host(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int, host_rgba8: *mut u8) -> c_int;
+    fn rtce_camera_rotation(yaw: f32, pitch: f32, rot_xyzw: *mut f32) -> c_int;
+    fn rtce_camera_pose(yaw: f32, pitch: f32, local_delta: *const f32, inout: *mut PushConstantData) -> c_int;
+    fn rtce_comm_unique_id(id_out_128: *mut c_void) -> c_int;
+    fn rtce_comm_init(ctx: *mut rtce_ctx, id_128: *const c_void, rank: c_int, world: c_int) -> c_int;
+    fn rtce_host_band_rows(height: c_int, world: c_int, rank: c_int, y0: *mut c_int, y1: *mut c_int) -> c_int;
+    fn rtce_gather_accum(ctx: *mut rtce_ctx, dst: c_int, bands: *const c_int) -> c_int;
+    fn rtce_gather_frames(ctx: *mut rtce_ctx, dst: c_int, bands: *const c_int, frames: c_int) -> c_int;
+    fn rtce_gather_wait(ctx: *mut rtce_ctx) -> c_int;
+    fn rtce_readback_gathered(ctx: *mut rtce_ctx, host: *mut f32, pitch_bytes: usize) -> c_int;
+}
+
+pub const RTCE_COMM_ID_BYTES: usize = 128;
+
+/// `Data::rotation()` (src/main.rs:402-404) without glam: `Quat::from_rotation_z(-yaw) * Quat::from_rotation_x(pitch)`
+/// as `[x, y, z, w]`, evaluated in f32 by the library (rtce_camera_rotation).
+pub fn camera_rotation(yaw: f32, pitch: f32) -> [f32; 4] {
+    let mut q = [0f32; 4];
+    unsafe { rtce_camera_rotation(yaw, pitch, q.as_mut_ptr()) };
+    q
+}
+
+/// The per-frame camera update of src/main.rs:770-773: clamps the pitch, writes `pc.rot`, adds the rotated
+/// `local_delta` (x right, y forward, z up; `Data::position()`, main.rs:406-414) to `pc.pos`.
+pub fn camera_pose(yaw: f32, pitch: f32, local_delta: [f32; 3], pc: &mut PushConstantData) {
+    unsafe { rtce_camera_pose(yaw, pitch, local_delta.as_ptr(), pc) };
+}
+
+/// NCCL unique id for `ConeMarcher::comm_init` (rank 0 creates it, the host distributes the 128 bytes).
+pub fn comm_unique_id() -> Result<[u8; RTCE_COMM_ID_BYTES], Error> {
+    let mut id = [0u8; RTCE_COMM_ID_BYTES];
+    let st = unsafe { rtce_comm_unique_id(id.as_mut_ptr() as *mut c_void) };
+    if st != 0 {
+        return Err(Error { status: st, message: "rtce_comm_unique_id (libnccl.so.2 not found?)".to_string() });
+    }
+    Ok(id)
+}
+
+/// Rows `[y0, y1)` of a `height`-row final level owned by `rank` of `world` (whole 8-row dispatch rows, compute.glsl:5).
+pub fn band_rows(height: i32, world: i32, rank: i32) -> (i32, i32) {
+    let (mut y0, mut y1) = (0, 0);
+    unsafe { rtce_host_band_rows(height, world, rank, &mut y0, &mut y1) };
+    (y0, y1)
 }
 
 #[derive(Debug)]
@@ -163,14 +207,14 @@ impl ConeMarcher {
     }
 
     /// Frames in flight (src/main.rs:859-884): `w` batches rotate over `w` windows of frame slots
-    /// (RTCE_OPT_FRAMES_IN_FLIGHT = 9); 1 = strict stream order.
+    /// (RTCE_OPT_FRAMES_IN_FLIGHT = 9); default 6; 1 = strict stream order.
     pub fn set_frames_in_flight(&mut self, w: u32) -> Result<(), Error> {
         let st = unsafe { rtce_set_option(self.ctx, 9, w as i64) };
         self.check(st)
     }
 
-    /// Kernel for scenes of more than 8 spheres (RTCE_OPT_LARGE_KERNEL = 12): 0 auto, 1 shared-memory version,
-    /// 2 register version.  No counterpart in the reference (utilities.glsl:3 caps MAX_OBJECTS at 8).
+    /// Kernel for scenes of more than 8 spheres (RTCE_OPT_LARGE_KERNEL = 12): 0 auto, 2 register version,
+    /// 3 event-driven version.  No counterpart in the reference (utilities.glsl:3 caps MAX_OBJECTS at 8).
     pub fn set_large_scene_kernel(&mut self, k: u32) -> Result<(), Error> {
         let st = unsafe { rtce_set_option(self.ctx, 12, k as i64) };
         self.check(st)
@@ -230,6 +274,53 @@ impl ConeMarcher {
         let st = unsafe { rtce_flush(self.ctx) };
         self.check(st)
     }
+
+    /// Pre-record: allocate every lane's frame slots and capture the launch graphs of a batch of `frames` frames now
+    /// (the reference re-records its command buffer every frame, src/main.rs:284-289, 886).
+    pub fn prepare(&mut self, frames: i32, accumulate: bool) -> Result<(), Error> {
+        let st = unsafe { rtce_prepare(self.ctx, frames, accumulate as c_int) };
+        self.check(st)
+    }
+
+    /// One loop body of src/main.rs:886-914 per frame, headless: compute pass, shading pass, RGBA8 frames to `out`
+    /// (`pcs.len() * view_w * view_h * 4` bytes).
+    pub fn render_rgba8(&mut self, pcs: &[PushConstantData], out: &mut [u8]) -> Result<(), Error> {
+        let st = unsafe { rtce_render_rgba8_to_host(self.ctx, pcs.as_ptr(), pcs.len() as c_int, out.as_mut_ptr()) };
+        self.check(st)
+    }
+
+    /// Several GPUs, one `ConeMarcher` per GPU (process or thread): join the communicator of `world` ranks.
+    pub fn comm_init(&mut self, id: &[u8; RTCE_COMM_ID_BYTES], rank: i32, world: i32) -> Result<(), Error> {
+        let st = unsafe { rtce_comm_init(self.ctx, id.as_ptr() as *const c_void, rank, world) };
+        self.check(st)
+    }
+
+    /// The one exchange of the accumulating path: every rank's row band of the accumulated image to rank `dst`
+    /// (grouped ncclSend / ncclRecv, in place), overlapping whatever is traced next.  `bands` = `[y0, y1]` per rank.
+    pub fn gather_accum(&mut self, dst: i32, bands: Option<&[[i32; 2]]>) -> Result<(), Error> {
+        let p = bands.map_or(std::ptr::null(), |b| b.as_ptr() as *const c_int);
+        let st = unsafe { rtce_gather_accum(self.ctx, dst, p) };
+        self.check(st)
+    }
+
+    /// The frame-by-frame form: the bands of frame slots `0 .. frames` of the latest batch, in place into `dst`'s slots.
+    pub fn gather_frames(&mut self, dst: i32, bands: Option<&[[i32; 2]]>, frames: i32) -> Result<(), Error> {
+        let p = bands.map_or(std::ptr::null(), |b| b.as_ptr() as *const c_int);
+        let st = unsafe { rtce_gather_frames(self.ctx, dst, p, frames) };
+        self.check(st)
+    }
+
+    /// Rank `dst`: the gathered image (waits for the exchange).
+    pub fn gathered(&mut self) -> Result<(usize, usize, Vec<f32>), Error> {
+        let (mut w, mut h) = (0, 0);
+        let mut p: *mut f32 = std::ptr::null_mut();
+        let st = unsafe { rtce_level_info(self.ctx, -1, 0, &mut w, &mut h, &mut p) };
+        self.check(st)?;
+        let mut out = vec![0f32; (w * h) as usize];
+        let st = unsafe { rtce_readback_gathered(self.ctx, out.as_mut_ptr(), 0) };
+        self.check(st)?;
+        Ok((w as usize, h as usize, out))
+    }
 }
 
 impl Drop for ConeMarcher {
@@ -272,15 +363,18 @@ impl Drop for PinnedF32 {
 
 /// Headless replacement of the reference's `main` loop body (src/main.rs:778-927 without window, swapchain and
 /// input): trace + shade one frame of the scene `mutable_data` (the bytes src/main.rs:524-605 builds) and return
-/// the RGBA8 image.  `rot` / `pos` are `data.rotation().to_array()` / `data.position.to_array()` (main.rs:770-773).
+/// the RGBA8 image.  The camera is the reference's own state (`Data::rotation`: yaw, pitch; the movement of this
+/// frame in camera axes), turned into push constants by `camera_pose` exactly as main.rs:770-773 does.
 pub fn render_headless(mutable_data: &[u8], width: f32, height: f32, fov: f32, render_dist: f32,
-                       rot: [f32; 4], pos: [f32; 3]) -> Result<(usize, usize, Vec<u8>), Error> {
+                       yaw: f32, pitch: f32, start_pos: [f32; 3], local_delta: [f32; 3])
+                       -> Result<(usize, usize, Vec<u8>), Error> {
     let mut m = ConeMarcher::new(0, render_dist)?;
     m.set_scene(mutable_data)?;
     let cb = ConstantBuffer { view: [width, height], ratio: [fov, fov * height / width] };   // main.rs:608-611
     m.set_view(&cb, 0)?;
-    let pc = PushConstantData { rot, pos, iter: 0, imageSize: [0.0; 2] };
-    m.trace(&pc)?;                                   // compute half, main.rs:291-316
-    m.shade_batch(std::slice::from_ref(&pc))?;       // render-pass half, main.rs:318-338
-    m.color_rgba8(0)
+    let mut pc = PushConstantData { rot: [0.0, 0.0, 0.0, 1.0], pos: start_pos, iter: 0, imageSize: [0.0; 2] };
+    camera_pose(yaw, pitch, local_delta, &mut pc);   // main.rs:770-773
+    let mut out = vec![0u8; (width as usize) * (height as usize) * 4];
+    m.render_rgba8(std::slice::from_ref(&pc), &mut out)?;   // main.rs:886-914: compute half, render-pass half, "present"
+    Ok((width as usize, height as usize, out))
 }

@@ -112,7 +112,54 @@ def test_rust_binding_source_matches_the_header():
         assert name in c_fns, f"{name} is not declared in include/rtce.h"
         assert (args.count(",") + 1 if args else 0) == c_fns[name], name
         n += 1
-    assert n >= 25
+    assert n >= 38
+
+
+def test_rust_binding_parameter_types_match_the_header():
+    """Beyond arity: every parameter (and the return type) of every extern in rust/rtce.rs maps to the C type the header
+    declares — `int` <-> c_int, `float` <-> f32, `size_t` <-> usize, `T*` <-> *mut T / *const T with the same constness."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = re.sub(r"/\*.*?\*/", "", open(os.path.join(root, "include", "rtce.h")).read(), flags=re.S)
+    base = {"int": "c_int", "float": "f32", "size_t": "usize", "int64_t": "i64", "uint32_t": "u32", "uint64_t": "u64",
+            "void": "c_void", "char": "c_char", "unsigned char": "u8", "rtce_ctx": "rtce_ctx",
+            "rtce_push_constants": "PushConstantData", "rtce_constant_buffer": "ConstantBuffer", "rtce_sphere": "Sphere",
+            "rtce_counters": "Counters", "double": "f64"}
+
+    def c_to_rust(t):
+        t = re.sub(r"\[\d*\]$", "*", t.strip())         # float out[2] -> float*
+        stars = t.count("*")
+        core = t.replace("*", " ").strip()
+        const = core.startswith("const ")
+        core = core[6:].strip() if const else core
+        r = base[core]
+        for i in range(stars):
+            r = ("*const " if (const and i == 0) else "*mut ") + r
+        return r
+
+    c_sig = {}
+    for m in re.finditer(r"^\s*((?:const\s+)?[a-z_0-9]+\s*\**)\s*(rtce_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", hdr, flags=re.S | re.M):
+        ret, name, args = m.group(1).strip(), m.group(2), m.group(3).strip()
+        params = []
+        if args not in ("", "void"):
+            for a in args.split(","):
+                a = " ".join(a.split())
+                mm = re.match(r"(.*?)([A-Za-z_][A-Za-z_0-9]*)(\[\d*\])?$", a)   # type, name, optional array
+                params.append(c_to_rust(mm.group(1) + (mm.group(3) or "")))
+        c_sig[name] = (None if ret == "void" else c_to_rust(ret), params)
+    rs = open(os.path.join(root, "rust", "rtce.rs")).read()
+    block = rs[rs.index('extern "C" {'):]
+    block = re.sub(r"//.*", "", block[:block.index("\n}")])
+    n = 0
+    for m in re.finditer(r"fn\s+(rtce_[a-z0-9_]+)\s*\((.*?)\)\s*(?:->\s*([^;]+))?;", block, flags=re.S):
+        name, args, ret = m.group(1), m.group(2).strip(), (m.group(3) or "").strip() or None
+        got = [" ".join(a.split(":", 1)[1].split()) for a in args.split(",")] if args else []
+        want_ret, want = c_sig[name]
+        # pointers to pointers: the header's T** is *mut *mut T on the Rust side
+        assert got == want, (name, got, want)
+        assert ret == want_ret, (name, ret, want_ret)
+        n += 1
+    assert n >= 38
 
 
 def test_header_compiles_as_c11_and_links_against_the_library(tmp_path):
