@@ -134,8 +134,9 @@ class Oracle:
         self._image_size(levels, i, view_w, view_h, o)
         return np.array([o[0], o[1]], dtype=np.float32)
 
-    def trace(self, spheres, view, ratio, rot, pos, render_dist=1000.0, levels=0, rect=None, threads=0):
-        """Run one frame.  Returns (list of per-level float32 arrays [h,w], counters dict)."""
+    def trace(self, spheres, view, ratio, rot, pos, render_dist=1000.0, levels=0, rect=None, threads=0, marcher=3):
+        """Run one frame.  Returns (list of per-level float32 arrays [h,w], counters dict).
+        marcher 1 / 2 (C port only): the author's alternative algorithms, restated from pseudo-code (unpinned)."""
         sph = np.ascontiguousarray(np.asarray(spheres, dtype=np.float32).reshape(-1, 4))
         view = np.ascontiguousarray(view, dtype=np.float32)
         ratio = np.ascontiguousarray(ratio, dtype=np.float32)
@@ -150,9 +151,19 @@ class Oracle:
         if rect is not None:
             rc = np.ascontiguousarray(rect, dtype=np.int32)
         cnt = (C.c_ulonglong * 3)()
-        err = self._trace(sph.ctypes.data, sph.shape[0], view.ctypes.data, ratio.ctypes.data, rot.ctypes.data,
-                          pos.ctypes.data, float(render_dist), levels, rc.ctypes.data if rc is not None else None,
-                          int(threads), ptrs, cnt)
+        if marcher != 3:
+            if self.kind != "port":
+                raise ValueError("marchers 1 and 2 exist only as a restatement (oracle 'port'): the reference ships pseudo-code")
+            fn = self.lib.rtce_oracle_trace_marcher
+            fn.restype = C.c_int
+            fn.argtypes = list(self._trace.argtypes) + [C.c_int]
+            err = fn(sph.ctypes.data, sph.shape[0], view.ctypes.data, ratio.ctypes.data, rot.ctypes.data,
+                     pos.ctypes.data, float(render_dist), levels, rc.ctypes.data if rc is not None else None,
+                     int(threads), ptrs, cnt, int(marcher))
+        else:
+            err = self._trace(sph.ctypes.data, sph.shape[0], view.ctypes.data, ratio.ctypes.data, rot.ctypes.data,
+                              pos.ctypes.data, float(render_dist), levels, rc.ctypes.data if rc is not None else None,
+                              int(threads), ptrs, cnt)
         if err != 0:
             raise RuntimeError(f"oracle[{self.kind}] trace failed: {err}")
         return imgs, {"R": int(cnt[0]), "E": int(cnt[1]), "S": int(cnt[2])}

@@ -96,6 +96,72 @@ static float trace_cone(v3 origin, v3 step, float threshold, const float* sphere
     return len;                                              /* :67 */
 }
 
+/* ---- the author's alternative marchers (shaders/tracing_algorithms.txt) -----------------------------------------
+ * The reference holds only PSEUDO-CODE for algorithms 1 and 2 (the shader ships algorithm 3): these are restatements of
+ * that text dropped into the traceCone frame of compute.glsl:34-68 (`len` is the text's `totalDist`, `threshold` its
+ * `thresholdDist`, `position` the frame's :45).  Parity of anything checked against them is UNPINNED by the reference.
+ * RTCE_ALT_MAX_TRIPS: the text has no trip limit; a ray still marching after that many trips is cut off here and in
+ * the kernels alike (it would hang the shader). */
+#define RTCE_ALT_MAX_TRIPS 65536u
+
+/* tracing_algorithms.txt:2-13  "algorithm 1: checks real distance for each object every update" */
+static float trace_cone_alg1(v3 origin, v3 step, float threshold, const float* spheres, uint32_t n,
+                             float render_dist, counters_t* cnt) {
+    float len = 0.0f;                                        /* frame :41 */
+    uint32_t trips = 0;
+    while (len < render_dist && trips++ < RTCE_ALT_MAX_TRIPS) {   /* frame :44 */
+        v3 position = { origin.x + step.x * len, origin.y + step.y * len, origin.z + step.z * len }; /* frame :45 */
+        float dist = sphere_sdf(position, spheres);          /* txt:2 */
+        for (uint32_t i = 1; i < n; i++) {                   /* txt:3-5 */
+            dist = f_min(dist, sphere_sdf(position, spheres + 4 * i));
+        }
+        cnt->E += n;
+        cnt->S++;
+        len += dist;                                         /* txt:7 */
+        float radius = (len + 1.0f) * threshold;             /* txt:8 */
+        if (dist <= radius) {                                /* txt:9-12 */
+            len -= radius;
+            break;
+        }
+    }
+    return len;
+}
+
+/* tracing_algorithms.txt:16-37  "algorithm 2: only checks real distance when necessary" */
+static float trace_cone_alg2(v3 origin, v3 step, float threshold, const float* spheres, uint32_t n,
+                             float render_dist, float* distances, counters_t* cnt) {
+    for (uint32_t i = 0; i < n; i++) {                       /* frame :37-39 */
+        distances[i] = sphere_sdf(origin, spheres + 4 * i);
+    }
+    cnt->E += n;
+    float len = 0.0f;
+    uint32_t closest = 0;                                    /* txt:19 OUTSIDE LOOP */
+    float nearest = 0.0f;                                    /* txt:20 */
+    uint32_t trips = 0;
+    while (len < render_dist && trips++ < RTCE_ALT_MAX_TRIPS) {
+        v3 position = { origin.x + step.x * len, origin.y + step.y * len, origin.z + step.z * len }; /* frame :45 */
+        for (uint32_t i = 0; i < n; i++) {                   /* txt:22-27, in this order */
+            distances[i] -= nearest;
+            if (distances[i] < distances[closest]) {
+                closest = i;
+            }
+        }
+        nearest = distances[closest];                        /* txt:29 */
+        len += nearest;                                      /* txt:30 */
+        distances[closest] = sphere_sdf(position, spheres + 4 * closest);   /* txt:31 */
+        cnt->E++;
+        cnt->S++;
+        float radius = (len + 1.0f) * threshold;             /* txt:33 */
+        if (distances[closest] <= radius) {                  /* txt:34-37 */
+            len += distances[closest] - radius;
+            break;
+        }
+    }
+    return len;
+}
+
+static int g_marcher = 3;   /* set by rtce_oracle_trace_marcher around one frame (callers are single-threaded tests) */
+
 /* compute.glsl:70-87  main() for one invocation (gx, gy) of level `iter`. */
 static float shade_pixel(uint32_t gx, uint32_t gy, uint32_t iter, const float image_size[2],
                          const float ratio[2], const float rot[4], const float pos[3],
@@ -119,7 +185,9 @@ static float shade_pixel(uint32_t gx, uint32_t gy, uint32_t iter, const float im
         len = parent[(size_t)(gy >> 1) * (size_t)parent_w + (size_t)(gx >> 1)];
     }
     v3 origin = { pos[0] + step.x * len, pos[1] + step.y * len, pos[2] + step.z * len };
-    len += trace_cone(origin, step, threshold, spheres, n, render_dist, distances, cnt);   /* :84 */
+    if (g_marcher == 1) len += trace_cone_alg1(origin, step, threshold, spheres, n, render_dist, cnt);
+    else if (g_marcher == 2) len += trace_cone_alg2(origin, step, threshold, spheres, n, render_dist, distances, cnt);
+    else len += trace_cone(origin, step, threshold, spheres, n, render_dist, distances, cnt);   /* :84 */
     return f_max(len, 0.0f);                                 /* :86 */
 }
 
@@ -200,4 +268,18 @@ RTCE_EXPORT int rtce_oracle_trace(const float* spheres, uint32_t n, const float*
         counters3[2] = S;
     }
     return 0;
+}
+
+/* The same frame with the author's alternative marchers (1, 2; 3 = the shipped algorithm).  objCount >= 1 for 1 and 2:
+ * algorithm 1 reads objs[0] unconditionally (tracing_algorithms.txt:2). */
+RTCE_EXPORT int rtce_oracle_trace_marcher(const float* spheres, uint32_t n, const float* view2, const float* ratio2,
+                                          const float* rot4, const float* pos3, float render_dist, int levels,
+                                          const int* rect4, int threads, float* const* level_out,
+                                          unsigned long long* counters3, int marcher) {
+    if (marcher < 1 || marcher > 3) return -6;
+    if (marcher != 3 && n < 1) return -6;
+    g_marcher = marcher;
+    const int r = rtce_oracle_trace(spheres, n, view2, ratio2, rot4, pos3, render_dist, levels, rect4, threads, level_out, counters3);
+    g_marcher = 3;
+    return r;
 }

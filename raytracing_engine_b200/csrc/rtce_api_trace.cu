@@ -108,7 +108,15 @@ int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int fr
         // other lanes (strips included) find room beside it; alone it takes every resident slot
         S.ctas_per_sm = c->strip_ctas_per_sm > 0 ? c->strip_ctas_per_sm : (crowd > 1 ? (crowd >= 4 ? 1 : 2) : 0);
         S.nty = (rc[3] - rc[1] + rows - 1) / rows;
+        S.two_pass = crowd > 1 ? 0 : 1;
         S.frames = frames;
+        {
+            const long long tiles = (long long)S.ntx * S.nty;
+            if (tiles > 0 && tiles < (1ll << 16) && tiles * frames < (1ll << 24)) {
+                S.magic_tiles = (1ull << 40) / (unsigned long long)tiles + 1ull;
+                S.magic_ntx = (1ull << 40) / (unsigned long long)S.ntx + 1ull;
+            }
+        }
         S.n_spheres = c->n_spheres;
         S.isx = isz[0]; S.isy = isz[1];
         S.ratx = c->cb.ratio[0]; S.raty = c->cb.ratio[1];
@@ -156,7 +164,8 @@ int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int fr
         if (kind == 0) memcpy(P.cam, cams, sizeof(Cam) * (size_t)frames);
         MarkScope mark(c, st, kind == 3 ? 3 : 0, i, g);
         e = kind == 3 ? launch_trace_level_pix(P, frames, c->count, st)
-                      : launch_trace_level_small(P, frames, c->count, st);   // main.rs:314 dispatch
+            : c->marcher != 3 ? launch_trace_level_alt(P, frames, c->count, c->marcher, st)
+                              : launch_trace_level_small(P, frames, c->count, st);   // main.rs:314 dispatch
     } else {
         LevelParamsLarge G{};
         G.out = base + c->loff[i];
@@ -175,7 +184,26 @@ int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int fr
         G.render_dist = c->render_dist;
         memcpy(G.cam, cams, sizeof(Cam) * (size_t)frames);
         if (c->n_spheres > large_reg_capacity()) return fail(c, RTCE_ERR_LIMIT, "more spheres than RTCE_MAX_SPHERES");
-        e = launch_trace_level_large_reg(G, frames, c->count, st);
+        if (c->large_mode != 3) {   // auto = the register kernel (the event-driven form is slower on BASELINE's scene: DESIGN.md)
+            e = launch_trace_level_large_reg(G, frames, c->count, st);
+        } else {
+            // event-driven kernel (+ the register kernel behind it for the rays it hands back); its scratch is sized
+            // for the largest launch of the view and allocated on first use (large scenes run in strict stream order)
+            const long long max_rays = (long long)c->lw[c->levels - 1] * c->lh[c->levels - 1] * std::min(c->slots, kMaxBatch);
+            const size_t need = large_ev_scratch_bytes(c->n_spheres, max_rays, nullptr);
+            if (c->large_state_bytes < need) {
+                RTCE_CUDA(c, cudaStreamSynchronize(st));
+                if (c->large_state) RTCE_CUDA(c, cudaFree(c->large_state));
+                c->large_state = nullptr;
+                c->large_state_bytes = 0;
+                cudaError_t em = cudaMalloc(&c->large_state, need);
+                if (em != cudaSuccess) return fail(c, RTCE_ERR_NOMEM, "cudaMalloc(event-driven kernel scratch)", em);
+                c->large_state_bytes = need;
+            }
+            const long long cap_rays = (long long)((c->large_state_bytes - large_ev_scratch_bytes(c->n_spheres, 0, nullptr)) / sizeof(int));
+            e = launch_trace_level_large_ev(G, frames, c->count, c->large_state, std::min(max_rays, cap_rays), st);
+            c->launches++;
+        }
     }
     if (e != cudaSuccess) return fail(c, RTCE_ERR_CUDA, "kernel launch", e);
     c->launches++;
@@ -383,7 +411,8 @@ int chunk_size(const rtce_ctx* c) { return std::min(c->slots, kMaxBatch); }
 
 // Lanes a call may use right now: counters and the debug timelines keep everything on the context's stream.
 int active_lanes(const rtce_ctx* c, int want) {
-    return (c->count || c->mark_launches || c->dbg_level >= 0) ? 1 : std::min(want, kMaxLanes);
+    // large scenes: a launch is hundreds of milliseconds of a full device and the kernels share one scratch area
+    return (c->count || c->mark_launches || c->dbg_level >= 0 || c->n_spheres > kSmallSceneMax) ? 1 : std::min(want, kMaxLanes);
 }
 
 // Windows for `nl` lanes, falling back to strict stream order when the device has no room for them.

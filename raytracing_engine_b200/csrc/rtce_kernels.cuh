@@ -64,6 +64,8 @@ cudaError_t launch_trace_level_small(const LevelParams& p, int frames, bool coun
 // Same dispatch for the coarse, latency-bound levels: 8x4 pixels per warp, branch-free march trips,
 // short correctly rounded sqrt.  Requires RENDER_DIST > 0.
 cudaError_t launch_trace_level_pix(const LevelParams& p, int frames, bool count, cudaStream_t st);
+// The author's alternative marchers (tracing_algorithms.txt: algorithm 1, algorithm 2) in the same frame; objCount 1..8.
+cudaError_t launch_trace_level_alt(const LevelParams& p, int frames, bool count, int marcher, cudaStream_t st);
 
 // Large scenes (objCount > 8, extension of utilities.glsl:3): spheres in global memory.
 struct LevelParamsLarge {
@@ -77,11 +79,20 @@ struct LevelParamsLarge {
     int iter;
     int n_spheres;
     float isx, isy, ratx, raty, threshold, render_dist;
+    const int* ray_list;          // nullptr = every ray of the rectangle; else ray indices (frame-major over the rectangle) ...
+    const unsigned* ray_count;    // ... and their number, both in device memory (register kernel only: the event-driven
+                                  // kernel's fallback list)
     Cam cam[kMaxBatch];
 };
 // The per-ray cache of lower bounds in registers (rtce_kernels_large_reg.cu); n_spheres <= large_reg_capacity().
 cudaError_t launch_trace_level_large_reg(const LevelParamsLarge& p, int frames, bool count, cudaStream_t st);
 int large_reg_capacity();
+// Event-driven form (rtce_kernels_large_ev.cu): one ray per warp, exact bounds only for the objects near in "time";
+// rays it cannot hold are traced by the register kernel from a fallback list (launched behind it on the same stream).
+// `scratch` = large_ev_scratch_bytes(n_spheres, max_rays) bytes of device memory, reusable by the next launch on the stream.
+size_t large_ev_scratch_bytes(int n_spheres, long long max_rays_per_launch, int* warps_out);
+cudaError_t launch_trace_level_large_ev(LevelParamsLarge p, int frames, bool count, void* scratch, long long max_rays,
+                                        cudaStream_t st);
 
 // ---- strip kernel (objCount <= 8): ONE level of a frame batch, persistent warps ---------------
 // The levels that hold almost all rays (the last three: 75 % + 19 % + 5 %) are each traced by one
@@ -105,9 +116,12 @@ struct StripParams {
     int w, pw;                // row pitch of this level and of the parent level
     int x0, y0, x1, y1;       // region of interest at this level
     int ntx, nty;             // tasks per frame: 32-wide columns x `rows`-high rows covering the ROI
+    unsigned long long magic_tiles, magic_ntx;   // floor(2^40 / d) + 1 for d = ntx * nty and d = ntx (0: divide): ticket decode
+                                                 // without integer division, exact while tasks < 2^24 and d < 2^16
     int rows;                 // rows per task, 1..kStripMaxRows
     int cta_share;            // launch 1/cta_share of the resident CTA slots (>= 1)
     int ctas_per_sm;          // > 0: launch at most this many CTAs per SM (leaves room for other lanes' launches)
+    int two_pass;             // 1: hot tiles first, the rest in a second walk of the tickets (a launch that owns the device)
     int frames;
     int n_spheres;
     float isx, isy, ratx, raty, threshold, render_dist;

@@ -54,7 +54,10 @@ __global__ void __launch_bounds__(kRegThreads, (G8 <= 5 ? 3 : 2))
     unsigned long long cE = 0, cS = 0, cR = 0;
     int parity = 0;   // runs across rays: consecutive block minima alternate buffers (one barrier per trip)
 
-    for (long long ray = blockIdx.x; ray < total_rays; ray += gridDim.x) {
+    const bool listed = P.ray_list != nullptr;   // the event-driven kernel's fallback rays
+    if (listed) total_rays = (long long)*P.ray_count;
+    for (long long idx = blockIdx.x; idx < total_rays; idx += gridDim.x) {
+        const long long ray = listed ? (long long)P.ray_list[idx] : idx;
         const int f = (int)(ray / per_frame);
         const long long rem = ray - (long long)f * per_frame;
         const int y = P.y0 + (int)(rem / rw);

@@ -487,7 +487,7 @@ def test_fast_math_is_correctly_rounded_exhaustively():
 # ---- BASELINE.json's own configs at full size (VERDICT r1 "Next round" #4) --------------------------------------
 
 @pytest.mark.parametrize("levels", [1, 4, 8])
-@pytest.mark.parametrize("large_kernel", [rt.LARGE_AUTO, rt.LARGE_REGISTER])
+@pytest.mark.parametrize("large_kernel", [rt.LARGE_AUTO, rt.LARGE_EVENT])
 def test_config3_ten_thousand_spheres_at_1080p_window(levels, large_kernel):
     """configs[3]: 10 000 synthetic spheres at 1920x1080, pyramid levels 1 / 4 / 8 (the "bounce-depth" axis), compared
     with the reference's shader text on a centred 256x144 window of EVERY level (rtce_set_rect / the checker's rect:
@@ -660,3 +660,58 @@ def test_render_rgba8_to_host_matches_shade_readback(shade_case_table):
             e.trace(pcs[k:k + 1])
             e.shade(pcs[k:k + 1])
             assert np.array_equal(out[k], e.readback_color_rgba8(0)), k
+
+
+@pytest.mark.parametrize("marcher", [1, 2])
+def test_alternative_marchers_match_their_restatement(marcher, case_table):
+    """RTCE_OPT_MARCHER 1 / 2: the author's algorithms 1 and 2 (shaders/tracing_algorithms.txt:2-13, :16-37) in the
+    traceCone frame.  The reference holds only pseudo-code for them, so the checker is the C restatement of that text
+    (oracle 'port'): parity UNPINNED by the reference.  Every level bit for bit, counters equal, on the golden case table's
+    scenes with 1..8 spheres and on the fuzz scenes; marcher 3 through the same entry point is the shipped algorithm."""
+    o = oracle.load("port")
+    names = ["default_800x600", "default_64x48", "default_250x130_resize_rule", "one_sphere_160x96", "eight_spheres_320x200",
+             "inside_sphere_200x120", "looking_back_320x200"]
+    for name in names:
+        (_, kind, sph, W, H, levels, rot, pos, keep) = case_table[name]
+        n = o.level_count(float(W), resize_rule=(levels == -1)) if levels <= 0 else levels
+        ref, cnt = o.trace(sph, [W, H], scene.view_ratio(W, H), rot, pos, 1000.0, n, marcher=marcher)
+        with rt.Engine(0, 1000.0) as e:
+            e.set_option(rt.OPT_MARCHER, marcher)
+            e.set_option(rt.OPT_COUNTERS, 1)
+            e.set_spheres(sph)
+            e.set_view(W, H, levels=levels)
+            e.trace(rt.make_push_constants([rot, rot], [pos, pos]))
+            for slot in (0, 1):
+                for i, b in enumerate(ref):
+                    assert np.array_equal(_bits(e.readback(i, slot)), _bits(b)), (name, marcher, slot, i)
+            c = e.counters()
+            assert {k: c[k] // 2 for k in "RES"} == cnt, (name, marcher)
+            e.set_option(rt.OPT_COUNTERS, 0)
+            e.trace(rt.make_push_constants([rot], [pos]))
+            assert np.array_equal(_bits(e.readback(-1, 0)), _bits(ref[-1])), (name, marcher, "uncounted")
+    rs = np.random.RandomState(4321)
+    for it in range(10):
+        nsp = int(rs.randint(1, 9))
+        sph = np.zeros((nsp, 4), np.float32)
+        sph[:, :3] = rs.uniform(-12, 12, (nsp, 3))
+        sph[:, 3] = rs.uniform(0.1, 4.0, nsp)
+        W, H = int(rs.randint(9, 300)), int(rs.randint(9, 200))
+        rot = camera.rotation(rs.uniform(-3.2, 3.2), rs.uniform(-1.5, 1.5))
+        pos = rs.uniform(-6, 6, 3).astype(np.float32)
+        ref, cnt = o.trace(sph, [W, H], scene.view_ratio(W, H), rot, pos, 1000.0, 0, marcher=marcher)
+        with rt.Engine(0, 1000.0) as e:
+            e.set_option(rt.OPT_MARCHER, marcher)
+            e.set_option(rt.OPT_COUNTERS, 1)
+            e.set_spheres(sph)
+            e.set_view(W, H)
+            e.trace(rt.make_push_constants([rot], [pos]))
+            for i, b in enumerate(ref):
+                assert np.array_equal(_bits(e.readback(i, 0)), _bits(b)), (it, marcher, i)
+            c = e.counters()
+            assert {k: c[k] for k in "RES"} == cnt, (it, marcher)
+    with rt.Engine(0, 1000.0) as e:                      # algorithm 1 reads objs[0]: an empty scene is refused, not guessed
+        e.set_option(rt.OPT_MARCHER, marcher)
+        e.set_spheres(np.zeros((0, 4), np.float32))
+        e.set_view(64, 48)
+        with pytest.raises(rt.RtceError):
+            e.trace(rt.make_push_constants([camera.IDENTITY_ROT], [[0, 0, 0]]))
