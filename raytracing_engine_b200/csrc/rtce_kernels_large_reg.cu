@@ -40,7 +40,11 @@ RTCE_DEV float min8(const float* v) {
     return fminf(fminf(fminf(v[0], v[1]), fminf(v[2], v[3])), fminf(fminf(v[4], v[5]), fminf(v[6], v[7])));
 }
 
-template <int G8, bool COUNT>
+// LISTED: the rays are the entries of P.ray_list (the event-driven kernel's fallback rays) and their number is read
+// from device memory.  A template parameter, not a run-time test: with the test in the loop ptxas kept the list
+// pointers live across the march loop and the G8 = 5 kernel went from 20 to 104 bytes of spills (0.87 -> 1.09 s per
+// configs[3] frame).
+template <int G8, bool COUNT, bool LISTED>
 __global__ void __launch_bounds__(kRegThreads, (G8 <= 5 ? 3 : 2))
     k_trace_level_large_reg(const __grid_constant__ LevelParamsLarge P, long long total_rays) {
     constexpr int NJ = 8 * G8;
@@ -54,10 +58,9 @@ __global__ void __launch_bounds__(kRegThreads, (G8 <= 5 ? 3 : 2))
     unsigned long long cE = 0, cS = 0, cR = 0;
     int parity = 0;   // runs across rays: consecutive block minima alternate buffers (one barrier per trip)
 
-    const bool listed = P.ray_list != nullptr;   // the event-driven kernel's fallback rays
-    if (listed) total_rays = (long long)*P.ray_count;
+    if (LISTED) total_rays = (long long)*P.ray_count;
     for (long long idx = blockIdx.x; idx < total_rays; idx += gridDim.x) {
-        const long long ray = listed ? (long long)P.ray_list[idx] : idx;
+        const long long ray = LISTED ? (long long)P.ray_list[idx] : idx;
         const int f = (int)(ray / per_frame);
         const long long rem = ray - (long long)f * per_frame;
         const int y = P.y0 + (int)(rem / rw);
@@ -144,10 +147,15 @@ static cudaError_t launch_g8(const LevelParamsLarge& p, long long total, bool co
     const int per_sm = G8 <= 5 ? 3 : 2;
     long long grid = (long long)sms * per_sm;   // persistent CTAs: one resident wave
     if (grid > total) grid = total;
-    if (count)
-        k_trace_level_large_reg<G8, true><<<(unsigned)grid, kRegThreads, 0, st>>>(p, total);
+    const bool listed = p.ray_list != nullptr;
+    if (count && listed)
+        k_trace_level_large_reg<G8, true, true><<<(unsigned)grid, kRegThreads, 0, st>>>(p, total);
+    else if (count)
+        k_trace_level_large_reg<G8, true, false><<<(unsigned)grid, kRegThreads, 0, st>>>(p, total);
+    else if (listed)
+        k_trace_level_large_reg<G8, false, true><<<(unsigned)grid, kRegThreads, 0, st>>>(p, total);
     else
-        k_trace_level_large_reg<G8, false><<<(unsigned)grid, kRegThreads, 0, st>>>(p, total);
+        k_trace_level_large_reg<G8, false, false><<<(unsigned)grid, kRegThreads, 0, st>>>(p, total);
     return cudaGetLastError();
 }
 

@@ -258,55 +258,11 @@ RTCE_DEV unsigned long long globaltimer_ns() {
 #ifndef RTCE_STRIP_MIN_BLOCKS
 #define RTCE_STRIP_MIN_BLOCKS 3
 #endif
-#ifndef RTCE_TICKET_DEPTH
-#define RTCE_TICKET_DEPTH 2      // ticket atomics in flight per warp (one ticket each: handing out 2 or 4 tickets per atomic
-                                 // unbalanced the end of the launch: final level of configs[1] alone 0.188 -> 0.218 -> 0.285 ms)
-#endif
-
-// A decoded ticket with the parent texels that classify it, fetched ONE TASK AHEAD of its use: the chain
-// ticket -> decode -> parent loads -> vote is ~1500 cycles of dependent latency in front of tasks that are as short
-// as ~170 instructions (whole-task far misses: 71 % of the final level's tasks); issued a task early it is covered
-// by the previous task's work.
-struct StripTask {
-    int f, tx, ty;      // frame, tile column / row
-    int second;         // which walk of the ticket range this ticket belongs to
-};
-
 // n / d for n * d < 2^40 (tasks < 2^24, divisors < 2^16: every view up to 8K x 32 frames) by one 64-bit multiply with
-// m = floor(2^40 / d) + 1 from the host; exact in that range (error term n (m d - 2^40) < 2^40).
+// m = floor(2^40 / d) + 1 from the host; exact in that range (error term n (m d - 2^40) < 2^40).  Only used when the
+// library is built with -DRTCE_STRIP_MAGIC_DIV (measured: no gain over the two 32-bit divisions, which are hidden
+// behind the ticket atomic).
 RTCE_DEV unsigned div_magic(unsigned n, unsigned long long m) { return (unsigned)(((unsigned long long)n * m) >> 40); }
-
-RTCE_DEV StripTask strip_task_decode(const StripParams& P, const int ticket, const int tasks, const int tiles) {
-    StripTask t;
-    t.second = ticket >= tasks ? 1 : 0;
-    const unsigned task = (unsigned)(ticket - t.second * tasks);
-    unsigned f, tile, ty;
-    if (P.magic_tiles) {
-        f = div_magic(task, P.magic_tiles);
-        tile = task - f * (unsigned)tiles;
-        ty = div_magic(tile, P.magic_ntx);
-    } else {
-        f = task / (unsigned)tiles;
-        tile = task - f * (unsigned)tiles;
-        ty = tile / (unsigned)P.ntx;
-    }
-    t.f = (int)f;
-    t.ty = (int)ty;
-    t.tx = (int)(tile - ty * (unsigned)P.ntx);
-    return t;
-}
-
-// The parent texels that classify a task (the lane's column at the task's first / last row pair), fetched one task
-// ahead of their use.  Only these two values stay live across the previous task's work; the ticket is decoded again
-// when the task starts (a dozen instructions) rather than kept in registers.
-RTCE_DEV float2 strip_task_prefetch(const StripParams& P, const int ticket, const int tasks, const int tiles, const int lane) {
-    const StripTask t = strip_task_decode(P, ticket, tasks, tiles);
-    const int xc = min(P.x0 + t.tx * 32 + lane, P.x1 - 1);
-    const int yb = P.y0 + t.ty * P.rows;
-    const int rows = min(P.rows, P.y1 - yb);
-    const float* pp = P.parent + ((size_t)t.f * P.slot_stride + (size_t)(yb >> 1) * P.pw + (xc >> 1));
-    return make_float2(__ldg(pp), __ldg(pp + (size_t)(((yb + rows - 1) >> 1) - (yb >> 1)) * P.pw));
-}
 
 template <int N, bool COUNT, bool HAS_PARENT>
 __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS : 2))
@@ -351,59 +307,58 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
     unsigned cR = 0, cE = 0, cS = 0, cF = 0;   // cF: rays resolved by the far-miss shortcut (a subset of cR)
     int qn = 0;   // warp-uniform
 
-    // Tasks (frame-major) are handed out dynamically: march cost differs by > 5x between tiles that cover spheres
-    // and tiles that see only background.  One atomic per ticket, issued RTCE_TICKET_DEPTH tasks ahead of its use (3552
-    // warps on one counter made the wait for the ticket 16 % of the stall samples), and every ticket is decoded and
-    // its classifying parent texels fetched one task ahead (strip_task_prefetch).  With a parent
-    // level and the device to itself (P.two_pass) the ticket range is walked TWICE: the first walk takes only the tiles
-    // whose parent texels show a hit ("hot": second trips, tail marches), the second walk the rest, whose cost is small
-    // and uniform, so the launch ends without a ragged tail of expensive tiles (longest-processing-time-first scheduling
+    // Tasks (frame-major) are handed out dynamically, one atomic per task fetched one task ahead: march cost differs
+    // by > 5x between tiles that cover spheres and tiles that see only background.  With a parent level and the
+    // device to itself (P.two_pass) the ticket range is walked TWICE: the first walk takes only the tiles whose
+    // parent texels show a hit ("hot": second trips, tail marches), the second walk the rest, whose cost is small and
+    // uniform, so the launch ends without a ragged tail of expensive tiles (longest-processing-time-first scheduling
     // with a two-class estimate).  With other lanes' launches running beside it the ragged end is filled by them and
-    // the second walk only costs (every ticket fetched, decoded and classified twice): one walk, +7 % throughput.
-    const bool kTwoPass = HAS_PARENT && P.two_pass != 0;
-    const int tickets_total = kTwoPass ? 2 * tasks : tasks;
+    // the second walk only costs (every ticket fetched, decoded and classified twice): one walk.
+    // Measured and rejected (profiles/r02_strip_variants.md): tickets issued 2 tasks ahead, the classifying parent
+    // texels fetched one task ahead, 2 or 4 tickets per atomic, division-free decode — each faster on some stall
+    // counter, none faster in batches per second with six lanes in flight.
+    const bool two_pass = HAS_PARENT && P.two_pass != 0;
+    const int tickets_total = two_pass ? 2 * tasks : tasks;
     int ticket = blockIdx.x * (kStripThreads / 32) + warp;   // the first round is static
-    int tk[RTCE_TICKET_DEPTH] = {};                           // lane 0: the tickets after it, oldest first
-    if (lane == 0 && ticket < tickets_total) {                // (a warp without work takes no tickets)
-#pragma unroll
-        for (int d = 0; d < RTCE_TICKET_DEPTH; d++) tk[d] = atomicAdd(P.tickets, 1) + nwarps;
-    }
+    int next = 0;
     unsigned long long t0 = 0, t1 = 0;
     int ndone = 0;
     if (P.dbg) t0 = globaltimer_ns();
-    float2 cls = make_float2(1.0f, 1.0f);   // compute.glsl:79 without a parent level
-    if (HAS_PARENT && ticket < tickets_total) cls = strip_task_prefetch(P, ticket, tasks, tiles, lane);
     while (ticket < tickets_total) {
-        // the ticket after this one, and its task, before this task's work
-        const int nticket = __shfl_sync(RTCE_FULL, tk[0], 0);
-#pragma unroll
-        for (int d = 0; d + 1 < RTCE_TICKET_DEPTH; d++) tk[d] = tk[d + 1];
-        if (lane == 0) tk[RTCE_TICKET_DEPTH - 1] = atomicAdd(P.tickets, 1) + nwarps;
-        float2 ncls = make_float2(1.0f, 1.0f);
-        if (HAS_PARENT && nticket < tickets_total) ncls = strip_task_prefetch(P, nticket, tasks, tiles, lane);
-
-        const StripTask cur = strip_task_decode(P, ticket, tasks, tiles);
-        const int second = cur.second;
-        const int f = cur.f;
-        const int x = P.x0 + cur.tx * 32 + lane;
+        if (lane == 0) next = atomicAdd(P.tickets, 1) + nwarps;
+        const int second = ticket >= tasks ? 1 : 0;
+        const unsigned task = (unsigned)(ticket - second * tasks);
+#ifdef RTCE_STRIP_MAGIC_DIV
+        const unsigned uf = div_magic(task, P.magic_tiles), tile = task - uf * (unsigned)tiles;
+        const unsigned uty = div_magic(tile, P.magic_ntx);
+#else
+        const unsigned uf = task / (unsigned)tiles, tile = task - uf * (unsigned)tiles;
+        const unsigned uty = tile / (unsigned)P.ntx;
+#endif
+        const int f = (int)uf, ty = (int)uty, tx = (int)(tile - uty * (unsigned)P.ntx);
+        const int x = P.x0 + tx * 32 + lane;
         const bool xok = x < P.x1;
         const int xc = min(x, P.x1 - 1);   // lanes past the region repeat its last column and store nothing
-        const int yb = P.y0 + cur.ty * P.rows;
+        const int yb = P.y0 + ty * P.rows;
         const int rows = min(P.rows, P.y1 - yb);
         // :80-82  rows 2k and 2k+1 share the parent texel; it is fetched one row pair ahead
         const float* pp = nullptr;
-        float start = cls.x, ahead = 0.0f;
+        float start = 1.0f, ahead = 0.0f;   // compute.glsl:79
         int pairs_left = 0;                 // parent rows still to fetch after `ahead`
-        bool skip = false;
         if (HAS_PARENT) {
             pp = P.parent + ((size_t)f * P.slot_stride + (size_t)(yb >> 1) * P.pw + (xc >> 1));
             pairs_left = ((yb + rows - 1) >> 1) - (yb >> 1);
-            const int hot = __any_sync(RTCE_FULL, start < rd || cls.y < rd) ? 1 : 0;   // a parent ray stopped on a sphere
-            if (kTwoPass && hot == second) skip = true;   // not this walk's class
+            start = __ldg(pp);
+            const float bottom = __ldg(pp + (size_t)pairs_left * P.pw);
+            const int hot = __any_sync(RTCE_FULL, start < rd || bottom < rd) ? 1 : 0;   // a parent ray stopped on a sphere
+            if (two_pass && hot == second) {   // not this walk's class
+                ticket = __shfl_sync(RTCE_FULL, next, 0);
+                continue;
+            }
             // Whole task a far miss (most of the background): every parent texel of the task is at least the camera's
             // far-miss distance away, so every ray is start + RENDER_DIST (see the row loop).  All parent rows are
             // fetched at once — row by row this path would be a chain of dependent loads.
-            if (!skip && !hot && !(yb & 1) && pairs_left < kFarPairs) {
+            if (!hot && !(yb & 1) && pairs_left < kFarPairs) {
                 const float tf = __ldg(reinterpret_cast<const float*>(P.cams + f) + 7);
                 float pv[kFarPairs];
 #pragma unroll
@@ -420,12 +375,12 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
                         if (COUNT) { cR += (unsigned)rows; cE += (unsigned)(N * rows); cS += (unsigned)rows; cF += (unsigned)rows; }
                     }
                     ndone++;
-                    skip = true;
+                    ticket = __shfl_sync(RTCE_FULL, next, 0);
+                    continue;
                 }
             }
-            if (!skip && pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
+            if (pairs_left > 0) { pp += P.pw; ahead = __ldg(pp); pairs_left--; }
         }
-        if (!skip) {
         ndone++;
         int budget = kTailBudget;   // of this task
         Cam cam;
@@ -489,9 +444,7 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
                 }
             }
         }
-        }   // !skip
-        ticket = nticket;
-        cls = ncls;
+        ticket = __shfl_sync(RTCE_FULL, next, 0);
     }
     if (P.dbg) t1 = globaltimer_ns();
     int budget = kTailBudget;
