@@ -121,11 +121,12 @@ typedef enum rtce_option {
                                    RENDER_DIST (host-side conservative bound per camera) is resolved as start + RENDER_DIST
                                    without evaluating an SDF: exactly what compute.glsl:37-66 computes for it (all
                                    distances[i] >= RENDER_DIST -> one trip, no hit).  0 = evaluate every ray in full. */
-    RTCE_OPT_LARGE_KERNEL = 12, /* objCount > 8 (extension of utilities.glsl:3): 0 (default) = auto (the event-driven kernel);
+    RTCE_OPT_LARGE_KERNEL = 12, /* objCount > 8 (extension of utilities.glsl:3): 0 (default) = auto = the register kernel;
                                    2 = register kernel (per-ray cache of lower bounds as an unrolled register array, every
-                                   bound touched on every trip; the second opinion of the parity tests);
-                                   3 = event-driven kernel (per-ray bounds in a calendar over the ray length: a trip touches
-                                   only the objects that can be due or be the minimum).  Both hold RTCE_MAX_SPHERES. */
+                                   bound touched on every trip);
+                                   3 = event-driven kernel (a trip touches only the objects that can be due or be the
+                                   minimum; exact, but slower on BASELINE.json configs[3] whose long rays dominate: DESIGN.md
+                                   "Large scenes"; the second opinion of the parity tests).  Both hold RTCE_MAX_SPHERES. */
     RTCE_OPT_MARCHER = 13       /* 3 (default) = tracing algorithm 3, the one compute.glsl:44-66 ships; 1, 2 = the author's
                                    alternatives (shaders/tracing_algorithms.txt:2-13 and :16-37) dropped into the same
                                    traceCone frame.  The reference holds only pseudo-code for 1 and 2: their checker is a
@@ -291,6 +292,25 @@ int rtce_debug_strip_timeline(rtce_ctx* ctx, int level, uint64_t* out, int max_w
  * on); a later call writes 6 doubles per launch {start ms, end ms, kind (1 strip, 2 overflow, 10 fused),
  * level, frame group, 0} and returns how many; it stays armed while max_launches > 0.  Synchronises. */
 int rtce_debug_launch_timeline(rtce_ctx* ctx, double* out, int max_launches);
+
+/* ---- allocation-free variant ----------------------------------------------------------------------------------
+ * rtce_trace_noalloc has NO counterpart in the reference: it was added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * It traces `frames` (1..RTCE_NOALLOC_MAX_FRAMES) frames of a scene of at most 8 spheres (host array, n x
+ * {x, y, z, size}) through all `levels` pyramid levels (0 = the startup rule of rtce_set_view) with the strip kernel on
+ * `cuda_stream` of `device`, asynchronously, and needs no context.  The caller owns inputs and outputs: d_pyramid is
+ * DEVICE memory, frame f at d_pyramid + f * frame_stride floats, its levels packed back to back in level order (level i =
+ * w_i * h_i floats, row pitch w_i, dims from rtce_host_level_dims; frame_stride >= their sum; frames * frame_stride
+ * < 2^32).  The kernel's scratch (task tickets, overflow queue, cameras: about 2.4 MB) is a static device array inside
+ * the library: every GPU that loads librtce.so holds it until the process exits; the call itself performs no
+ * cudaMalloc / cudaFree / allocating library call.  All calls share that array: what must start at zero is cleared on
+ * the stream at the head of every call, and calls that OVERLAP on one GPU race on it (keep them in stream order;
+ * different GPUs are independent).  Sizes beyond the limits are rejected with RTCE_ERR_LIMIT.  On failure the
+ * message is written to `err` (may be NULL).  Texels are bit-identical to rtce_trace_batch + rtce_readback. */
+#define RTCE_NOALLOC_MAX_FRAMES 16
+int rtce_trace_noalloc(int device, void* cuda_stream, const float* spheres, int n_spheres, const rtce_constant_buffer* cb,
+                       int levels, float render_dist, const rtce_push_constants* pcs, int frames, float* d_pyramid,
+                       size_t frame_stride, char* err, size_t err_len);
 
 #ifdef __cplusplus
 }

@@ -9,7 +9,7 @@ from .engine import (Engine, PinnedBuffer, RtceError, PUSH_CONSTANTS_DTYPE, make
                      host_level_count, host_level_dims, host_image_size, LIB_PATH, measure_fp32_issue, selftest_math,
                      OPT_COUNTERS, OPT_FRAME_SLOTS, OPT_KERNEL, OPT_STRIP_MIN_RAYS, OPT_GROUPS, OPT_STRIP_ROWS, OPT_GRAPH,
                      OPT_FRAMES_IN_FLIGHT, OPT_STRIP_CTAS_PER_SM, OPT_FAR_MISS, OPT_LARGE_KERNEL, OPT_MARCHER, KERNEL_AUTO,
-                     KERNEL_PER_LEVEL, KERNEL_STRIP, LARGE_AUTO, LARGE_REGISTER, LARGE_EVENT, ABI_VERSION, selftest_repeat,
+                     KERNEL_PER_LEVEL, KERNEL_STRIP, LARGE_AUTO, LARGE_REGISTER, LARGE_EVENT, ABI_VERSION, selftest_repeat, trace_noalloc,
                      camera_rotation, camera_pose, host_band_rows, comm_unique_id)
 from . import scene, camera
 

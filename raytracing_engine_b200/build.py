@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(PKG_DIR, "librtce.so")
 OBJ_DIR = os.path.join(PKG_DIR, "build")
 SOURCES = ["rtce_api.cu", "rtce_api_trace.cu", "rtce_comm.cu", "rtce_camera.cu", "rtce_kernels.cu", "rtce_kernels_accum.cu",
            "rtce_kernels_large_reg.cu", "rtce_kernels_large_ev.cu", "rtce_kernels_strip.cu", "rtce_kernels_shade.cu",
-           "rtce_measure.cu"]
+           "rtce_measure.cu", "rtce_noalloc.cu"]
 DEPS = ["rtce_ctx.hpp", "rtce_device.cuh", "rtce_march.cuh", "rtce_shade_math.cuh", "rtce_kernels.cuh", "rtce_host.hpp",
         "../../include/rtce.h"]
 

@@ -35,7 +35,7 @@ PUSH_CONSTANTS_DTYPE = np.dtype(
 assert PUSH_CONSTANTS_DTYPE.itemsize == 40
 
 EXPORTS = [
-    "rtce_abi_version", "rtce_create", "rtce_destroy", "rtce_last_error", "rtce_status_string",
+    "rtce_trace_noalloc", "rtce_abi_version", "rtce_create", "rtce_destroy", "rtce_last_error", "rtce_status_string",
     "rtce_set_option", "rtce_set_stream", "rtce_set_scene", "rtce_set_spheres", "rtce_set_view",
     "rtce_set_rect", "rtce_level_count", "rtce_level_info", "rtce_host_level_count",
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
@@ -127,6 +127,7 @@ def load_library() -> C.CDLL:
         "rtce_selftest_math": (i32, [i32, C.POINTER(C.c_uint64)]),
         "rtce_debug_strip_timeline": (i32, [vp, i32, vp, i32]),
         "rtce_debug_launch_timeline": (i32, [vp, vp, i32]),
+        "rtce_trace_noalloc": (i32, [i32, vp, vp, i32, vp, i32, f32, vp, i32, vp, sz, C.c_char_p, sz]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -230,6 +231,27 @@ def comm_unique_id() -> bytes:
     if rc != RTCE_OK:
         raise RtceError(f"rtce_comm_unique_id: {rc} (libnccl.so.2 not found?)")
     return buf.raw
+
+
+def trace_noalloc(device: int, stream_ptr, spheres, view_w: float, view_h: float, pcs, d_pyramid: int, frame_stride: int,
+                  fov: float = 1.0, levels: int = 0, render_dist: float = 1000.0, ratio=None) -> None:
+    """rtce_trace_noalloc (include/rtce.h; no counterpart in the reference): the strip-kernel pass with its scratch in a
+    static device array - no device allocation.  `d_pyramid` is a DEVICE address the caller owns (frames x frame_stride
+    floats, levels packed back to back); asynchronous on `stream_ptr`.  Raises RtceError with the library's message."""
+    w, h, fov = np.float32(view_w), np.float32(view_h), np.float32(fov)
+    if ratio is None:
+        ratio = (fov, np.float32(np.float32(fov * h) / w))
+    cb = np.array([w, h, ratio[0], ratio[1]], dtype=np.float32)
+    sph = np.ascontiguousarray(spheres, dtype=np.float32).reshape(-1, 4)
+    pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
+    err = C.create_string_buffer(256)
+    rc = load_library().rtce_trace_noalloc(int(device), C.c_void_p(stream_ptr or 0), sph.ctypes.data, int(sph.shape[0]), cb.ctypes.data,
+                                           int(levels), float(render_dist), pcs.ctypes.data, int(pcs.size), C.c_void_p(int(d_pyramid)),
+                                           int(frame_stride), err, len(err))
+    if rc != RTCE_OK:
+        e = RtceError(f"{err.value.decode()} ({rc})")
+        e.code = rc
+        raise e
 
 
 def make_push_constants(rots, poss) -> np.ndarray:
