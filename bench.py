@@ -516,6 +516,22 @@ def strong_c4(cx: Ctx):
                 eng.trace_accumulate(pcs)
                 ms = cx.max_over_ranks(cx.timed(lambda: eng.trace_accumulate(pcs), 1))
             trials.append((hw, ms, cb))
+        # measured-cost balancing on top of the best estimate: time every rank on its band, cut bands of equal predicted
+        # time (sharding.rebalanced_bands), keep the result only if the slowest rank got faster
+        if len(cands) > 1:
+            cb = min(trials, key=lambda t: t[1])[2]
+            for it in range(3):
+                eng.set_rect(0, cb[cx.rank][0], Wf, cb[cx.rank][1])
+                eng.prepare(wl["frames"], accumulate=True)
+                eng.trace_accumulate(pcs)
+                t_rank = cx.gather_floats(cx.timed(lambda: eng.trace_accumulate(pcs), 2) / 2)
+                if it > 0:
+                    trials.append((f"measured-{it}", max(t_rank), cb))
+                cb = sharding.rebalanced_bands(cb, t_rank, Hf)
+            eng.set_rect(0, cb[cx.rank][0], Wf, cb[cx.rank][1])
+            eng.prepare(wl["frames"], accumulate=True)
+            eng.trace_accumulate(pcs)
+            trials.append(("measured-3", cx.max_over_ranks(cx.timed(lambda: eng.trace_accumulate(pcs), 2) / 2), cb))
         hw, trial_ms, bands = min(trials, key=lambda t: (t[1] is None, t[1] or 0.0)) if len(trials) > 1 else trials[0]
         y0, y1 = bands[cx.rank]
         eng.set_rect(0, y0, Wf, y1)
@@ -555,7 +571,7 @@ def strong_c4(cx: Ctx):
             "gather_bytes_into_rank0": int((Hf - (bands[0][1] - bands[0][0])) * Wf * 4), "gather_check": check,
             "gather": "rtce_gather_accum: grouped ncclSend / ncclRecv inside librtce.so, bands received in place, on a communication "
                       "stream out of a staging copy: the gather of step k overlaps the tracing of step k + 1; the timed region ends after the last gather",
-            "bands": {"rows_per_rank": [b1 - b0 for b0, b1 in bands], "marched_texel_weight": hw,
+            "bands": {"rows_per_rank": [b1 - b0 for b0, b1 in bands], "cut_by": hw if isinstance(hw, str) else f"estimate, marched-texel weight {hw}",
                       "set_up_trials_ms_per_step": {str(t[0]): t[1] for t in trials}},
             "lanes": f"{lanes} chunks of {slots} frames in flight"}
 

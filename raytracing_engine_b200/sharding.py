@@ -55,6 +55,21 @@ def weighted_bands(row_weights, world: int, align: int = BAND_ALIGN):
     return [(min(a * align, height), min(b * align, height)) for a, b in zip(cuts, cuts[1:])]
 
 
+def rebalanced_bands(bands, times, height: int, align: int = BAND_ALIGN):
+    """One step of measured-cost balancing: given the bands of a trial and the time each rank took for its band,
+    cut new bands of equal PREDICTED time, taking the cost of a row to be uniform inside its old band
+    (t_r / rows_r).  Every rank holds the same `times` (gathered), so every rank computes the same cuts.  The
+    estimate ignores the part of a rank's time that does not scale with its rows (the coarse levels), so the caller
+    times the result and keeps it only if it is faster."""
+    import numpy as np
+    assert len(bands) == len(times) and bands[0][0] == 0 and bands[-1][1] == height
+    w = np.zeros(height, dtype=np.float64)
+    for (y0, y1), t in zip(bands, times):
+        if y1 > y0:
+            w[y0:y1] = max(float(t), 0.0) / (y1 - y0)
+    return weighted_bands(w, len(bands), align)
+
+
 def row_cost(final_level: torch.Tensor, render_dist: float, hit_weight: float):
     """Estimated cost of each final-level row from one traced frame [rows, width]: a texel that reached
     RENDER_DIST is background (resolved by the far-miss shortcut: a load, a compare and a store), anything else

@@ -85,6 +85,22 @@ def test_banded_trace_plus_gather_is_bit_identical(world, W, H):
     assert q.get(timeout=5) is True
 
 
+def test_rebalanced_bands_move_rows_to_the_faster_ranks():
+    """Measured-cost balancing (bench.py strong_c4): ranks that took longer give rows away, cuts stay on multiples of 8,
+    the bands still tile the image, and equal times change nothing beyond rounding."""
+    H = 4320
+    bands = sharding.all_bands(H, 8)
+    times = [26.3, 26.0, 26.3, 26.2, 25.4, 25.2, 24.6, 23.6]          # the N = 8 run of round 2
+    nb = sharding.rebalanced_bands(bands, times, H)
+    assert nb[0][0] == 0 and nb[-1][1] == H and all(a[1] == b[0] for a, b in zip(nb, nb[1:]))
+    assert all(y0 % 8 == 0 and y1 > y0 for y0, y1 in nb)
+    assert nb[0][1] - nb[0][0] < bands[0][1] - bands[0][0] and nb[-1][1] - nb[-1][0] > bands[-1][1] - bands[-1][0]
+    pred = [t / (b[1] - b[0]) * (n[1] - n[0]) for t, b, n in zip(times, bands, nb)]   # crude: same per-row cost per rank
+    assert max(pred) < max(times)
+    same = sharding.rebalanced_bands(bands, [5.0] * 8, H)
+    assert all(abs(a[0] - b[0]) <= 8 and abs(a[1] - b[1]) <= 8 for a, b in zip(same, bands))
+
+
 def test_weighted_bands_balance_cost_in_multiples_of_8():
     rs = np.random.RandomState(7)
     for H in (136, 600, 1080, 4320):
