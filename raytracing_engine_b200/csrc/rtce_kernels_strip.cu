@@ -258,10 +258,19 @@ RTCE_DEV unsigned long long globaltimer_ns() {
 #ifndef RTCE_STRIP_MIN_BLOCKS
 #define RTCE_STRIP_MIN_BLOCKS 3
 #endif
+// Compile-time switches of the per-ticket path (all on; 0 restores the round-1 form for A/B runs).  ncu of the final
+// level (profiles/r02_v9_strip_final_level_hot_blocks.txt): fetching and decoding a ticket was 120 instructions x
+// 130 560 tickets = 14.5 % of the launch's instructions and a third of its stall samples, the whole-task far-miss path
+// another 7.5 %.
+#ifndef RTCE_STRIP_MAGIC
+#define RTCE_STRIP_MAGIC 1      // ticket -> (frame, tile row, tile column) by two 64-bit multiplies instead of two divisions
+#endif
+#ifndef RTCE_STRIP_FARFAST
+#define RTCE_STRIP_FARFAST 1    // whole-task far miss of a full-height task: loads and stores at constant row offsets
+#endif
+
 // n / d for n * d < 2^40 (tasks < 2^24, divisors < 2^16: every view up to 8K x 32 frames) by one 64-bit multiply with
-// m = floor(2^40 / d) + 1 from the host; exact in that range (error term n (m d - 2^40) < 2^40).  Only used when the
-// library is built with -DRTCE_STRIP_MAGIC_DIV (measured: no gain over the two 32-bit divisions, which are hidden
-// behind the ticket atomic).
+// m = floor(2^40 / d) + 1 from the host; exact in that range (error term n (m d - 2^40) < 2^40).  m = 0: divide.
 RTCE_DEV unsigned div_magic(unsigned n, unsigned long long m) { return (unsigned)(((unsigned long long)n * m) >> 40); }
 
 template <int N, bool COUNT, bool HAS_PARENT>
@@ -315,8 +324,8 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
     // with a two-class estimate).  With other lanes' launches running beside it the ragged end is filled by them and
     // the second walk only costs (every ticket fetched, decoded and classified twice): one walk.
     // Measured and rejected (profiles/r02_strip_variants.md): tickets issued 2 tasks ahead, the classifying parent
-    // texels fetched one task ahead, 2 or 4 tickets per atomic, division-free decode — each faster on some stall
-    // counter, none faster in batches per second with six lanes in flight.
+    // texels fetched one task ahead, 2 or 4 tickets per atomic — each faster on some stall counter, none faster in
+    // batches per second with six lanes in flight.
     const bool two_pass = HAS_PARENT && P.two_pass != 0;
     const int tickets_total = two_pass ? 2 * tasks : tasks;
     int ticket = blockIdx.x * (kStripThreads / 32) + warp;   // the first round is static
@@ -325,16 +334,19 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
     int ndone = 0;
     if (P.dbg) t0 = globaltimer_ns();
     while (ticket < tickets_total) {
-        if (lane == 0) next = atomicAdd(P.tickets, 1) + nwarps;
+        if (lane == 0) next = atomicAdd(P.tickets, 1) + nwarps;   // (ptxas wraps it in warp-aggregation code, also as inline PTX)
         const int second = ticket >= tasks ? 1 : 0;
         const unsigned task = (unsigned)(ticket - second * tasks);
-#ifdef RTCE_STRIP_MAGIC_DIV
-        const unsigned uf = div_magic(task, P.magic_tiles), tile = task - uf * (unsigned)tiles;
-        const unsigned uty = div_magic(tile, P.magic_ntx);
-#else
-        const unsigned uf = task / (unsigned)tiles, tile = task - uf * (unsigned)tiles;
-        const unsigned uty = tile / (unsigned)P.ntx;
-#endif
+        unsigned uf, tile, uty;
+        if (RTCE_STRIP_MAGIC && P.magic_tiles != 0ull) {
+            uf = div_magic(task, P.magic_tiles);
+            tile = task - uf * (unsigned)tiles;
+            uty = div_magic(tile, P.magic_ntx);
+        } else {
+            uf = task / (unsigned)tiles;
+            tile = task - uf * (unsigned)tiles;
+            uty = tile / (unsigned)P.ntx;
+        }
         const int f = (int)uf, ty = (int)uty, tx = (int)(tile - uty * (unsigned)P.ntx);
         const int x = P.x0 + tx * 32 + lane;
         const bool xok = x < P.x1;
@@ -360,18 +372,29 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
             // fetched at once — row by row this path would be a chain of dependent loads.
             if (!hot && !(yb & 1) && pairs_left < kFarPairs) {
                 const float tf = __ldg(reinterpret_cast<const float*>(P.cams + f) + 7);
+                const bool full = RTCE_STRIP_FARFAST && rows == 2 * kFarPairs;   // a full-height task (warp-uniform); yb is even here
                 float pv[kFarPairs];
+                if (full) {
 #pragma unroll
-                for (int k = 0; k < kFarPairs; k++) pv[k] = k <= pairs_left ? __ldg(pp + (size_t)k * P.pw) : pv[0];
+                    for (int k = 0; k < kFarPairs; k++) pv[k] = __ldg(pp + (size_t)(k * P.pw));
+                } else {
+#pragma unroll
+                    for (int k = 0; k < kFarPairs; k++) pv[k] = k <= pairs_left ? __ldg(pp + (size_t)k * P.pw) : pv[0];
+                }
                 float nearest = pv[0];
 #pragma unroll
                 for (int k = 1; k < kFarPairs; k++) nearest = fminf(nearest, pv[k]);
                 if (__all_sync(RTCE_FULL, !xok || nearest >= tf)) {
                     if (xok) {
                         float* o = img + ((size_t)f * P.slot_stride + (size_t)yb * P.w + xc);
+                        if (full) {
 #pragma unroll
-                        for (int rr = 0; rr < 2 * kFarPairs; rr++)
-                            if (rr < rows) o[(size_t)rr * P.w] = fadd(pv[rr >> 1], rd);   // :84, :86 (positive)
+                            for (int rr = 0; rr < 2 * kFarPairs; rr++) o[(size_t)(rr * P.w)] = fadd(pv[rr >> 1], rd);   // :84, :86 (positive)
+                        } else {
+#pragma unroll
+                            for (int rr = 0; rr < 2 * kFarPairs; rr++)
+                                if (rr < rows) o[(size_t)rr * P.w] = fadd(pv[rr >> 1], rd);
+                        }
                         if (COUNT) { cR += (unsigned)rows; cE += (unsigned)(N * rows); cS += (unsigned)rows; cF += (unsigned)rows; }
                     }
                     ndone++;
