@@ -40,7 +40,7 @@ int lane_init(rtce_ctx* c, int l) {
         ok = cudaStreamCreateWithFlags(&L.grp_stream[g], cudaStreamNonBlocking) == cudaSuccess &&
              cudaEventCreateWithFlags(&L.ev_join[g], cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; ok && i < kCamRing; i++) ok = cudaEventCreateWithFlags(&L.ev_cam[i], cudaEventDisableTiming) == cudaSuccess;
-    ok = ok && cudaMalloc(&L.d_tickets, sizeof(int) * kMaxGroups * kMaxLevels * 4) == cudaSuccess &&
+    ok = ok && cudaMalloc(&L.d_tickets, sizeof(int) * kMaxGroups * kMaxLevels * kTicketWords) == cudaSuccess &&
          cudaMalloc(&L.d_cams, sizeof(Cam) * kMaxBatch) == cudaSuccess &&
          cudaMallocHost(&L.h_cams, sizeof(Cam) * kMaxBatch * kCamRing) == cudaSuccess &&
          cudaMalloc(&L.d_oq, sizeof(float) * kMaxGroups * (size_t)kOverflowCap * (10 + kSmallSceneMax)) == cudaSuccess;

@@ -78,7 +78,7 @@ void fill_cams(const rtce_ctx* c, Cam* cams, const rtce_push_constants* pcs, int
 // `crowd` = how many lanes trace side by side (0 or 1: this chain has the device to itself).
 int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int frames, float* base, int i, int kind, cudaStream_t st,
                  int g, int share = 1, int crowd = 0) {
-    int* const tickets = L.d_tickets + (size_t)g * kMaxLevels * 4;
+    int* const tickets = L.d_tickets + (size_t)g * kMaxLevels * kTicketWords;
     float isz[2];
     host_image_size(c->levels, i, c->cb.view[0], c->cb.view[1], isz);   // main.rs:303-305
     int rc[4];
@@ -90,9 +90,9 @@ int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int fr
         S.parent = i > 0 ? base + c->loff[i - 1] : nullptr;
         S.slot_stride = c->slot_stride;
         S.counters = c->d_counters + 4 * i;
-        S.tickets = tickets + 4 * i;
+        S.tickets = tickets + kTicketWords * i;
         S.oq = L.d_oq + (size_t)g * kOverflowCap * (10 + kSmallSceneMax);
-        S.oq_count = reinterpret_cast<unsigned*>(tickets + 4 * i + 1);
+        S.oq_count = reinterpret_cast<unsigned*>(tickets + kTicketWords * i + 1);
         S.oq_cap = kOverflowCap;
         S.dbg = (c->d_dbg && c->dbg_level == i && g == 0) ? c->d_dbg : nullptr;
         S.w = c->lw[i];
@@ -133,7 +133,7 @@ int launch_level(rtce_ctx* c, Lane& L, const Cam* cams, const Cam* dcams, int fr
             O.out = S.out;
             O.oq = S.oq;
             O.oq_count = S.oq_count;
-            O.oq_head = reinterpret_cast<unsigned*>(tickets + 4 * i + 2);
+            O.oq_head = reinterpret_cast<unsigned*>(tickets + kTicketWords * i + 2);
             O.oq_cap = S.oq_cap;
             O.counters = c->d_counters + 4 * i;
             O.n_spheres = c->n_spheres;
@@ -273,7 +273,7 @@ int emit_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const Cam* cams, int fram
         const int share = std::min(ng, 3);
         for (int g = 0; g < ng; g++) {
             if (k < c->levels)   // task counters / overflow cursors of this group's strip launches
-                RTCE_CUDA(c, cudaMemsetAsync(L.d_tickets + (size_t)g * kMaxLevels * 4, 0, sizeof(int) * kMaxLevels * 4, st[g]));
+                RTCE_CUDA(c, cudaMemsetAsync(L.d_tickets + (size_t)g * kMaxLevels * kTicketWords, 0, sizeof(int) * kMaxLevels * kTicketWords, st[g]));
         }
         for (int i = 0; i < k; i++)   // the coarse levels
             for (int g = 0; g < ng; g++)

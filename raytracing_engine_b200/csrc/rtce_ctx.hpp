@@ -45,7 +45,7 @@ struct Lane {
     cudaEvent_t ev_cam[kCamRing] = {};     // staging entry consumed
     unsigned cam_seq = 0;
     std::vector<ChunkGraph> graphs;
-    int* d_tickets = nullptr;    // [kMaxGroups][kMaxLevels][4] {task ticket, overflow count, overflow head, -}, zeroed per chunk
+    int* d_tickets = nullptr;    // [kMaxGroups][kMaxLevels][kTicketWords] {-, overflow count, overflow head, -, .., task counters}, zeroed per chunk
     float* d_oq = nullptr;       // overflow queues of the strip launches (kMaxGroups x kOverflowCap rays x 18 words)
 };
 

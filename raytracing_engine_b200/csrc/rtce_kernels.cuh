@@ -101,6 +101,15 @@ cudaError_t launch_trace_level_large_ev(LevelParamsLarge p, int frames, bool cou
 // trips are parked in a per-warp shared-memory queue that persists across the warp's tasks and
 // is marched with lane refill (DESIGN.md "Strip kernel").
 constexpr int kStripThreads = 256;
+// Task tickets of ONE strip launch.  A single global counter hands out at most one ticket per ~0.72 ns however many warps
+// ask (same-address atomics serialise in L2: tools/probes/atomic_ticket_probe.cu, 130 560 tickets = 93 us, more than
+// half of the final-level launch), so the ticket space is STRIPED over kTicketCounters counters, one 128-byte line
+// each: counter k hands out tickets k, k + K, k + 2K, ... — all counters advance through the ticket space together,
+// which keeps the global order (hot tiles first) — a warp draws from its home counter (warp index mod K) and, once
+// that is exhausted, from the others in turn.
+constexpr int kTicketCounters = 16;
+constexpr int kTicketStride = 32;     // ints between counters
+constexpr int kTicketWords = 32 + kTicketCounters * kTicketStride;   // per launch: {-, overflow count, overflow head, -, ...} + the counters
 constexpr int kStripMaxRows = 32;      // rows per task (row-term table size)
 
 struct StripParams {
@@ -108,7 +117,7 @@ struct StripParams {
     const float* parent;      // level-1 image of frame slot 0; nullptr at level 0 (start = 1.0)
     size_t slot_stride;       // floats between frame slots (frames * slot_stride < 2^32: queue offsets are 32-bit)
     unsigned long long* counters;
-    int* tickets;             // zero-initialised task counter of this launch
+    int* tickets;             // zero-initialised kTicketWords block of this launch (counters from word 32)
     float* oq;                // overflow queue: rays that outlive kMaxAge trips in a warp's tail go here (nullptr = none)
     unsigned* oq_count;       // zero-initialised number of rays in oq
     unsigned oq_cap;          // capacity of oq in rays; word w of ray k is oq[w * oq_cap + k]

@@ -34,6 +34,10 @@ constexpr int kPinWords = 40;       // per-warp scratch for pinning uniforms (>=
 #ifndef RTCE_TAIL_BUDGET
 #define RTCE_TAIL_BUDGET (1 << 30)
 #endif
+#ifndef RTCE_TICKET_PROBE
+#define RTCE_TICKET_PROBE 3
+#endif
+constexpr int kTicketProbe = RTCE_TICKET_PROBE;   // counters a warp draws from before it leaves (its own + the next ones)
 constexpr int kFarPairs = 8;        // parent rows of a task the far-miss fast path handles (16 rows per task)
 constexpr int kMaxAge = RTCE_MAX_AGE;   // tail trips after which a ray is evicted to the overflow queue
 constexpr int kTailBudget = RTCE_TAIL_BUDGET;   // tail trips a warp spends on ONE task before it evicts every tail ray it
@@ -328,13 +332,36 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
     // batches per second with six lanes in flight.
     const bool two_pass = HAS_PARENT && P.two_pass != 0;
     const int tickets_total = two_pass ? 2 * tasks : tasks;
-    int ticket = blockIdx.x * (kStripThreads / 32) + warp;   // the first round is static
+    // Tickets: the first round is static (warp index); the rest come from kTicketCounters striped counters
+    // (rtce_kernels.cuh), fetched one task ahead from the warp's current counter.
+    const int wglobal = blockIdx.x * (kStripThreads / 32) + warp;
+    int* const tcount = P.tickets + 32;
+    // every stripe is drained by its home warps, so each counter needs some: a small grid uses one counter
+    const int kc = nwarps >= 8 * kTicketCounters ? kTicketCounters : 1;
+    const int probe = min(kTicketProbe, kc);
+    int cur = wglobal & (kc - 1);   // warp-uniform; moves on when the counter's stripe is exhausted
+    int tried = 1;                               // counters this warp has drawn from
     int next = 0;
     unsigned long long t0 = 0, t1 = 0;
     int ndone = 0;
     if (P.dbg) t0 = globaltimer_ns();
-    while (ticket < tickets_total) {
-        if (lane == 0) next = atomicAdd(P.tickets, 1) + nwarps;   // (ptxas wraps it in warp-aggregation code, also as inline PTX)
+    // `continue` below runs the increment: the prefetched ticket, or — once the current counter is past the end of its
+    // stripe — a ticket from the next counter; a warp leaves after it has seen kTicketProbe counters exhausted (the
+    // stripes interleave the tasks and 222 warps share each, so they run out within a few tasks of each other: probing
+    // all 16 would be 15 dependent atomics of pure latency at the end of every warp)
+    auto draw = [&](int from) { return nwarps + atomicAdd(tcount + from * kTicketStride, 1) * kc + from; };
+    auto advance = [&]() {
+        int t = __shfl_sync(RTCE_FULL, next, 0);
+        while (t >= tickets_total && tried < probe) {
+            tried++;
+            cur = (cur + 1) & (kc - 1);
+            if (lane == 0) next = draw(cur);
+            t = __shfl_sync(RTCE_FULL, next, 0);
+        }
+        return t;
+    };
+    for (int ticket = wglobal; ticket < tickets_total; ticket = advance()) {
+        if (lane == 0) next = draw(cur);
         const int second = ticket >= tasks ? 1 : 0;
         const unsigned task = (unsigned)(ticket - second * tasks);
         unsigned uf, tile, uty;
@@ -360,19 +387,19 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
         if (HAS_PARENT) {
             pp = P.parent + ((size_t)f * P.slot_stride + (size_t)(yb >> 1) * P.pw + (xc >> 1));
             pairs_left = ((yb + rows - 1) >> 1) - (yb >> 1);
-            start = __ldg(pp);
-            const float bottom = __ldg(pp + (size_t)pairs_left * P.pw);
-            const int hot = __any_sync(RTCE_FULL, start < rd || bottom < rd) ? 1 : 0;   // a parent ray stopped on a sphere
-            if (two_pass && hot == second) {   // not this walk's class
-                ticket = __shfl_sync(RTCE_FULL, next, 0);
-                continue;
-            }
-            // Whole task a far miss (most of the background): every parent texel of the task is at least the camera's
-            // far-miss distance away, so every ray is start + RENDER_DIST (see the row loop).  All parent rows are
-            // fetched at once — row by row this path would be a chain of dependent loads.
-            if (!hot && !(yb & 1) && pairs_left < kFarPairs) {
+            // Classification and the whole-task far miss read the SAME parent texels, so they are fetched in ONE round trip:
+            // the task's (up to) 8 parent rows of this lane's column and the camera's far-miss distance.  (Fetched as
+            // first / last row for the class and then all rows for the far miss, a background task was two dependent L2
+            // round trips around ~150 instructions: with 6 warps per scheduler that is 0.6 instructions per cycle, which
+            // is what ncu measured for the whole launch.)
+            //   hot  = a parent ray of the task stopped on a sphere (second trips, tail marches: the expensive class);
+            //   far  = every parent texel is at least the camera's far-miss distance away, so every ray of the task is
+            //          start + RENDER_DIST (see the row loop): 71 % of the final level's rays.
+            const bool farshape = !(yb & 1) && pairs_left < kFarPairs;   // warp-uniform: the task's rows are whole pairs, <= 8 of them
+            int hot;
+            if (farshape) {
                 const float tf = __ldg(reinterpret_cast<const float*>(P.cams + f) + 7);
-                const bool full = RTCE_STRIP_FARFAST && rows == 2 * kFarPairs;   // a full-height task (warp-uniform); yb is even here
+                const bool full = RTCE_STRIP_FARFAST && rows == 2 * kFarPairs;   // a full-height task (warp-uniform)
                 float pv[kFarPairs];
                 if (full) {
 #pragma unroll
@@ -381,10 +408,15 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
 #pragma unroll
                     for (int k = 0; k < kFarPairs; k++) pv[k] = k <= pairs_left ? __ldg(pp + (size_t)k * P.pw) : pv[0];
                 }
+                start = pv[0];
                 float nearest = pv[0];
 #pragma unroll
                 for (int k = 1; k < kFarPairs; k++) nearest = fminf(nearest, pv[k]);
-                if (__all_sync(RTCE_FULL, !xok || nearest >= tf)) {
+                hot = __any_sync(RTCE_FULL, nearest < rd) ? 1 : 0;
+                if (two_pass && hot == second) {   // not this walk's class
+                    continue;
+                }
+                if (!hot && __all_sync(RTCE_FULL, !xok || nearest >= tf)) {
                     if (xok) {
                         float* o = img + ((size_t)f * P.slot_stride + (size_t)yb * P.w + xc);
                         if (full) {
@@ -398,7 +430,13 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
                         if (COUNT) { cR += (unsigned)rows; cE += (unsigned)(N * rows); cS += (unsigned)rows; cF += (unsigned)rows; }
                     }
                     ndone++;
-                    ticket = __shfl_sync(RTCE_FULL, next, 0);
+                    continue;
+                }
+            } else {   // odd first row or a taller task (RTCE_OPT_STRIP_ROWS > 16): class from the first and last parent row
+                start = __ldg(pp);
+                const float bottom = __ldg(pp + (size_t)pairs_left * P.pw);
+                hot = __any_sync(RTCE_FULL, start < rd || bottom < rd) ? 1 : 0;
+                if (two_pass && hot == second) {
                     continue;
                 }
             }
@@ -467,7 +505,6 @@ __global__ void __launch_bounds__(kStripThreads, (N <= 4 ? RTCE_STRIP_MIN_BLOCKS
                 }
             }
         }
-        ticket = __shfl_sync(RTCE_FULL, next, 0);
     }
     if (P.dbg) t1 = globaltimer_ns();
     int budget = kTailBudget;

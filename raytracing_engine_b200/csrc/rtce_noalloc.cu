@@ -36,7 +36,7 @@ constexpr unsigned kNoAllocOqCap = 1u << 15;   // rays of the overflow queue; be
 constexpr int kOqWords = 10 + kSmallSceneMax;  // words per queued ray (rtce_kernels_strip.cu)
 
 struct NoAllocScratch {
-    int tickets[kMaxLevels][4];                // {task ticket, overflow count, overflow head, -} per level
+    int tickets[kMaxLevels][kTicketWords];     // {-, overflow count, overflow head, -, .., task counters} per level
     Cam cams[kNoAllocFrames];                  // the frames' cameras, read by the strip kernel from device memory
     float oq[(size_t)kNoAllocOqCap * kOqWords];
 };
@@ -54,7 +54,7 @@ struct NoAllocSetup {
 __global__ void k_noalloc_setup(const __grid_constant__ NoAllocSetup S) {
     NoAllocScratch* sc = reinterpret_cast<NoAllocScratch*>(g_noalloc_scratch);
     const int t = threadIdx.x;
-    if (t < kMaxLevels * 4) (&sc->tickets[0][0])[t] = 0;
+    for (int k = t; k < kMaxLevels * kTicketWords; k += blockDim.x) (&sc->tickets[0][0])[k] = 0;
     constexpr int kCamWords = (int)(sizeof(Cam) / sizeof(float));
     for (int k = t; k < S.frames * kCamWords; k += blockDim.x)
         reinterpret_cast<float*>(sc->cams)[k] = reinterpret_cast<const float*>(S.cams)[k];
