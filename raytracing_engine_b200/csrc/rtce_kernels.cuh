@@ -100,7 +100,10 @@ cudaError_t launch_trace_level_large_ev(LevelParamsLarge p, int frames, bool cou
 // level; a lane keeps one image column for the whole task.  Rays that need more than two march
 // trips are parked in a per-warp shared-memory queue that persists across the warp's tasks and
 // is marched with lane refill (DESIGN.md "Strip kernel").
-constexpr int kStripThreads = 256;
+#ifndef RTCE_STRIP_THREADS
+#define RTCE_STRIP_THREADS 256
+#endif
+constexpr int kStripThreads = RTCE_STRIP_THREADS;
 // Task tickets of ONE strip launch.  A single global counter hands out at most one ticket per ~0.72 ns however many warps
 // ask (same-address atomics serialise in L2: tools/probes/atomic_ticket_probe.cu, 130 560 tickets = 93 us, more than
 // half of the final-level launch), so the ticket space is STRIPED over kTicketCounters counters, one 128-byte line
