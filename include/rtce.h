@@ -209,10 +209,19 @@ int rtce_get_shade_counters(rtce_ctx* ctx, uint64_t out[4]);
  * and copy every frame's final level to `host_out` (frames * w * h floats), copies overlapped
  * with the tracing of later frames.  Synchronises before returning. */
 int rtce_render_to_host(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames, float* host_out);
+/* The same for a caller that streams batches into two (or more) host buffers, the way the reference keeps frames in
+ * flight behind its swapchain (main.rs:859-884: submit frame k, wait for the fence of frame k - 1): everything of this
+ * call is enqueued, then the host waits for the PREVIOUS rtce_render_to_host_async call only.  When call k returns, the
+ * frames of call k - 1 are complete in the buffer that call was given, and the device is working on call k.  rtce_sync
+ * completes the last call.  `pcs` is consumed during the call; `host_out` must stay valid until the next call (or
+ * rtce_sync) returns, and should be page-locked (rtce_host_alloc) or the copies serialise. */
+int rtce_render_to_host_async(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames, float* host_out);
 /* The headless replacement of one reference frame loop body (main.rs:886-914: compute half, render-pass half, present):
  * trace `frames` frames, shade them (fragment.glsl) and copy every frame's RGBA8 UNORM image (window size, 4 bytes per
  * pixel) to `host_rgba8` (frames * view_w * view_h * 4 bytes).  Synchronises before returning. */
 int rtce_render_rgba8_to_host(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames, unsigned char* host_rgba8);
+/* Asynchronous form, same contract as rtce_render_to_host_async (the two share the double buffering and may alternate). */
+int rtce_render_rgba8_to_host_async(rtce_ctx* ctx, const rtce_push_constants* pcs, int frames, unsigned char* host_rgba8);
 /* Page-locked host buffers for rtce_render_to_host / rtce_readback (pageable memory works, slower). */
 int rtce_host_alloc(void** out, size_t nbytes);
 int rtce_host_free(void* p);

@@ -92,6 +92,10 @@ int flush_lanes(rtce_ctx* c) {
 int quiesce(rtce_ctx* c) {
     int r = flush_lanes(c);
     if (r) return r;
+    if (c->host_copies_pending) {   // frames of rtce_render_to_host_async still on their way to host memory
+        RTCE_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+        c->host_copies_pending = false;
+    }
     RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
     return RTCE_OK;
 }
@@ -175,6 +179,7 @@ int rtce_create(int device, float render_dist, rtce_ctx** out) {
     for (int i = 0; i < 2; i++) {
         cudaEventCreateWithFlags(&c->ev_traced[i], cudaEventDisableTiming);
         cudaEventCreateWithFlags(&c->ev_copied[i], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&c->ev_host_done[i], cudaEventDisableTiming);
     }
     c->stream = c->own_stream;
     *out = c;
@@ -193,6 +198,7 @@ void rtce_destroy(rtce_ctx* c) {
     for (int i = 0; i < 2; i++) {
         if (c->ev_traced[i]) cudaEventDestroy(c->ev_traced[i]);
         if (c->ev_copied[i]) cudaEventDestroy(c->ev_copied[i]);
+        if (c->ev_host_done[i]) cudaEventDestroy(c->ev_host_done[i]);
     }
     if (c->d_pyr) cudaFree(c->d_pyr);
     if (c->d_accum) cudaFree(c->d_accum);

@@ -392,12 +392,20 @@ int trace_chunk(rtce_ctx* c, int lane, cudaStream_t ls, const rtce_push_constant
     return RTCE_OK;
 }
 
-int check_ready(rtce_ctx* c, const void* p, int frames) {
+// `keep_host_copies`: the caller is rtce_render_to_host(_async) itself, which orders its own reuse of window 0 behind
+// the copies half by half; every other tracer first makes the context's stream wait for copies that may still read it.
+int check_ready(rtce_ctx* c, const void* p, int frames, bool keep_host_copies = false) {
     if (!c) return RTCE_ERR_INVALID;
     if (!p || frames < 1) return fail(c, RTCE_ERR_INVALID, "null push constants or frames < 1");
     if (!c->have_scene || !c->have_view) return fail(c, RTCE_ERR_STATE, "set scene and view before tracing");
     if (c->marcher != 3 && (c->n_spheres < 1 || c->n_spheres > kSmallSceneMax))
         return fail(c, RTCE_ERR_INVALID, "RTCE_OPT_MARCHER 1 / 2 need 1 <= objCount <= 8 (algorithm 1 reads objs[0])");
+    if (c->host_copies_pending && !keep_host_copies) {
+        DeviceGuard g(c->device);
+        for (int i = 0; i < 2; i++)
+            if (c->half_used[i]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[i], 0));
+        c->host_copies_pending = false;
+    }
     return RTCE_OK;
 }
 
@@ -791,8 +799,29 @@ int rtce_host_alloc(void** out, size_t nbytes) {
 
 int rtce_host_free(void* p) { return cudaFreeHost(p) == cudaSuccess ? RTCE_OK : RTCE_ERR_CUDA; }
 
-int rtce_render_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames, float* host_out) {
-    int r = check_ready(c, pcs, frames);
+// End of a rtce_render_*_to_host(_async) call: block for everything (synchronous form), or record this call's
+// completion on the copy stream and block for the PREVIOUS asynchronous call only.
+static int finish_host_call(rtce_ctx* c, bool wait) {
+    if (wait) {
+        RTCE_CUDA(c, cudaStreamSynchronize(c->copy_stream));
+        RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->host_copies_pending = false;
+        c->host_calls = 0;
+        return RTCE_OK;
+    }
+    const unsigned k = c->host_calls++;
+    RTCE_CUDA(c, cudaEventRecord(c->ev_host_done[k & 1], c->copy_stream));
+    if (k > 0) RTCE_CUDA(c, cudaEventSynchronize(c->ev_host_done[(k - 1) & 1]));
+    return RTCE_OK;
+}
+
+// `wait`: synchronise before returning (rtce_render_to_host).  Otherwise (rtce_render_to_host_async) everything of this
+// call is enqueued, then the host waits for the PREVIOUS asynchronous call only: when call k returns, the frames of call
+// k - 1 are in their host buffer while the device works on call k — a caller with two host buffers never drains the
+// pipeline between batches (the synchronous form idles the copy engine while the first half of every batch is traced,
+// and the SMs while the last half is copied).
+static int render_to_host_impl(rtce_ctx* c, const rtce_push_constants* pcs, int frames, float* host_out, bool wait) {
+    int r = check_ready(c, pcs, frames, true);
     if (r) return r;
     if (!host_out) return fail(c, RTCE_ERR_INVALID, "rtce_render_to_host: null output");
     DeviceGuard g(c->device);
@@ -810,11 +839,11 @@ int rtce_render_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames,
     const int half = std::max(1, std::min(c->slots / 2, kMaxBatch));
     const bool pingpong = c->slots >= 2;
     int phase = 0;
-    bool used[2] = {false, false};
     for (int f0 = 0; f0 < frames; f0 += half, phase ^= 1) {
         const int n = std::min(half, frames - f0);
         const int slot0 = pingpong ? phase * half : 0;
-        if (used[phase]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));   // half is free again
+        if (c->half_used[phase]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));   // half is free again
+        if (!pingpong && c->half_used[phase ^ 1]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase ^ 1], 0));   // one slot: both
         if ((r = trace_chunk(c, 0, c->stream, pcs + f0, n, slot0, 1, 0))) return r;
         RTCE_CUDA(c, cudaEventRecord(c->ev_traced[phase], c->stream));
         RTCE_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_traced[phase], 0));
@@ -825,20 +854,26 @@ int rtce_render_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames,
                                          c->copy_stream));
         }
         RTCE_CUDA(c, cudaEventRecord(c->ev_copied[phase], c->copy_stream));
-        used[phase] = true;
-        if (!pingpong) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));
+        c->half_used[phase] = true;
+        c->host_copies_pending = true;
     }
-    RTCE_CUDA(c, cudaStreamSynchronize(c->copy_stream));
-    RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
-    return RTCE_OK;
+    return finish_host_call(c, wait);
+}
+
+int rtce_render_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames, float* host_out) {
+    return render_to_host_impl(c, pcs, frames, host_out, true);
+}
+
+int rtce_render_to_host_async(rtce_ctx* c, const rtce_push_constants* pcs, int frames, float* host_out) {
+    return render_to_host_impl(c, pcs, frames, host_out, false);
 }
 
 // main.rs:886-914 headless: compute half (trace), render-pass half (shade), "present" (RGBA8 UNORM to host memory).
 // Chunks of min(slots, kMaxBatch) frames on the context's stream; the D2H copy of a chunk's RGBA8 images runs on the
 // copy stream under the tracing of the next chunk (the RGBA8 staging holds one image per slot: two chunks of
 // half the window alternate, as in rtce_render_to_host).
-int rtce_render_rgba8_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames, unsigned char* host_rgba8) {
-    int r = check_ready(c, pcs, frames);
+static int render_rgba8_impl(rtce_ctx* c, const rtce_push_constants* pcs, int frames, unsigned char* host_rgba8, bool wait) {
+    int r = check_ready(c, pcs, frames, true);
     if (r) return r;
     if (!host_rgba8) return fail(c, RTCE_ERR_INVALID, "rtce_render_rgba8_to_host: null output");
     if (!c->have_materials) return fail(c, RTCE_ERR_STATE, "rtce_render_rgba8_to_host: materials and lights come with rtce_set_scene");
@@ -850,11 +885,11 @@ int rtce_render_rgba8_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int f
     const bool pingpong = c->slots >= 2;
     const size_t img_bytes = c->d_color_px * sizeof(uchar4);
     int phase = 0;
-    bool used[2] = {false, false};
     for (int f0 = 0; f0 < frames; f0 += half, phase ^= 1) {
         const int n = std::min(half, frames - f0);
         const int slot0 = pingpong ? phase * half : 0;
-        if (used[phase]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));   // half is free again
+        if (c->half_used[phase]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));   // half is free again
+        if (!pingpong && c->half_used[phase ^ 1]) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase ^ 1], 0));   // one slot: both
         c->last_lane = 0;
         c->lanes_active = 1;
         if ((r = trace_chunk(c, 0, c->stream, pcs + f0, n, slot0, 1, 0))) return r;
@@ -868,12 +903,18 @@ int rtce_render_rgba8_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int f
         RTCE_CUDA(c, cudaMemcpyAsync(host_rgba8 + (size_t)f0 * img_bytes, c->d_rgba8 + (size_t)slot0 * c->d_color_px, img_bytes * (size_t)n,
                                      cudaMemcpyDeviceToHost, c->copy_stream));
         RTCE_CUDA(c, cudaEventRecord(c->ev_copied[phase], c->copy_stream));
-        used[phase] = true;
-        if (!pingpong) RTCE_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[phase], 0));
+        c->half_used[phase] = true;
+        c->host_copies_pending = true;
     }
-    RTCE_CUDA(c, cudaStreamSynchronize(c->copy_stream));
-    RTCE_CUDA(c, cudaStreamSynchronize(c->stream));
-    return RTCE_OK;
+    return finish_host_call(c, wait);
+}
+
+int rtce_render_rgba8_to_host(rtce_ctx* c, const rtce_push_constants* pcs, int frames, unsigned char* host_rgba8) {
+    return render_rgba8_impl(c, pcs, frames, host_rgba8, true);
+}
+
+int rtce_render_rgba8_to_host_async(rtce_ctx* c, const rtce_push_constants* pcs, int frames, unsigned char* host_rgba8) {
+    return render_rgba8_impl(c, pcs, frames, host_rgba8, false);
 }
 
 static int fetch_counters(rtce_ctx* c, unsigned long long* h /* [kMaxLevels][4] */) {

@@ -71,6 +71,12 @@ struct rtce_ctx {
     std::vector<LaunchMark> marks;
     cudaEvent_t ev_traced[2] = {nullptr, nullptr};
     cudaEvent_t ev_copied[2] = {nullptr, nullptr};
+    // rtce_render_to_host(_async): which half of window 0 has a copy outstanding or finished on the copy stream; the
+    // completion events of the last two asynchronous calls; whether copies may still be reading window 0
+    bool half_used[2] = {false, false};
+    cudaEvent_t ev_host_done[2] = {nullptr, nullptr};
+    unsigned host_calls = 0;
+    bool host_copies_pending = false;
     std::string err;
 
     // binding 1 (MutableData.objCount / objs)

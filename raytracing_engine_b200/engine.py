@@ -40,7 +40,7 @@ EXPORTS = [
     "rtce_set_rect", "rtce_level_count", "rtce_level_info", "rtce_host_level_count",
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
     "rtce_trace_accumulate", "rtce_accum_info", "rtce_prepare", "rtce_readback", "rtce_readback_accum",
-    "rtce_render_to_host", "rtce_render_rgba8_to_host", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_flush", "rtce_get_counters",
+    "rtce_render_to_host", "rtce_render_to_host_async", "rtce_render_rgba8_to_host", "rtce_render_rgba8_to_host_async", "rtce_host_alloc", "rtce_host_free", "rtce_sync", "rtce_flush", "rtce_get_counters",
     "rtce_get_level_counters", "rtce_get_far_miss_rays",
     "rtce_shade_batch", "rtce_color_info", "rtce_readback_color", "rtce_readback_color_rgba8", "rtce_get_shade_counters",
     "rtce_measure_fp32_issue", "rtce_selftest_math", "rtce_selftest_repeat", "rtce_debug_strip_timeline",
@@ -97,7 +97,9 @@ def load_library() -> C.CDLL:
         "rtce_readback": (i32, [vp, i32, i32, vp, sz]),
         "rtce_readback_accum": (i32, [vp, vp, sz]),
         "rtce_render_to_host": (i32, [vp, vp, i32, vp]),
+        "rtce_render_to_host_async": (i32, [vp, vp, i32, vp]),
         "rtce_render_rgba8_to_host": (i32, [vp, vp, i32, vp]),
+        "rtce_render_rgba8_to_host_async": (i32, [vp, vp, i32, vp]),
         "rtce_prepare": (i32, [vp, i32, i32]),
         "rtce_selftest_repeat": (i32, [i32, vp, vp, vp, sz]),
         "rtce_camera_rotation": (i32, [f32, f32, vp]),
@@ -484,6 +486,15 @@ class Engine:
                     "rtce_render_to_host")
         return out
 
+    def render_to_host_async(self, pcs: np.ndarray, out: np.ndarray) -> None:
+        """rtce_render_to_host_async: returns when the PREVIOUS asynchronous call's frames are in its buffer; `out`
+        (page-locked, e.g. PinnedBuffer.array) is complete after the next call or sync() returns."""
+        pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
+        w, h, _ = self.level_info(-1, 0)
+        assert out.dtype == np.float32 and out.size == pcs.shape[0] * h * w and out.flags["C_CONTIGUOUS"]
+        self._check(self.lib.rtce_render_to_host_async(self._ctx, pcs.ctypes.data, pcs.shape[0], out.ctypes.data),
+                    "rtce_render_to_host_async")
+
     def render_rgba8_to_host(self, pcs: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
         """Headless frame loop body (main.rs:886-914): trace + shade + RGBA8 UNORM images to host memory."""
         pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
@@ -494,6 +505,14 @@ class Engine:
         self._check(self.lib.rtce_render_rgba8_to_host(self._ctx, pcs.ctypes.data, pcs.shape[0], out.ctypes.data),
                     "rtce_render_rgba8_to_host")
         return out
+
+    def render_rgba8_to_host_async(self, pcs: np.ndarray, out: np.ndarray) -> None:
+        """rtce_render_rgba8_to_host_async: same contract as render_to_host_async, RGBA8 frames."""
+        pcs = np.ascontiguousarray(pcs, dtype=PUSH_CONSTANTS_DTYPE).reshape(-1)
+        vw, vh = int(self.view[0]), int(self.view[1])
+        assert out.dtype == np.uint8 and out.size == pcs.shape[0] * vh * vw * 4 and out.flags["C_CONTIGUOUS"]
+        self._check(self.lib.rtce_render_rgba8_to_host_async(self._ctx, pcs.ctypes.data, pcs.shape[0], out.ctypes.data),
+                    "rtce_render_rgba8_to_host_async")
 
     def strip_timeline(self, level: int = -1, max_warps: int = 8192, fetch: bool = True):
         """Diagnostics: arm / fetch the per-warp timeline of the strip launch that traces `level`."""

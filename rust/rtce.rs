@@ -72,6 +72,7 @@ extern "C" {
     fn rtce_trace_batch(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int) -> c_int;
     fn rtce_readback(ctx: *mut rtce_ctx, level: c_int, slot: c_int, host: *mut f32, pitch_bytes: usize) -> c_int;
     fn rtce_render_to_host(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int, host_out: *mut f32) -> c_int;
+    fn rtce_render_to_host_async(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int, host_out: *mut f32) -> c_int;
     fn rtce_sync(ctx: *mut rtce_ctx) -> c_int;
     fn rtce_flush(ctx: *mut rtce_ctx) -> c_int;
     fn rtce_get_counters(ctx: *mut rtce_ctx, out: *mut Counters) -> c_int;
@@ -86,6 +87,7 @@ extern "C" {
     fn rtce_host_free(p: *mut c_void) -> c_int;
     fn rtce_prepare(ctx: *mut rtce_ctx, frames: c_int, accumulate: c_int) -> c_int;
     fn rtce_render_rgba8_to_host(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int, host_rgba8: *mut u8) -> c_int;
+    fn rtce_render_rgba8_to_host_async(ctx: *mut rtce_ctx, pcs: *const PushConstantData, frames: c_int, host_rgba8: *mut u8) -> c_int;
     fn rtce_camera_rotation(yaw: f32, pitch: f32, rot_xyzw: *mut f32) -> c_int;
     fn rtce_camera_pose(yaw: f32, pitch: f32, local_delta: *const f32, inout: *mut PushConstantData) -> c_int;
     fn rtce_comm_unique_id(id_out_128: *mut c_void) -> c_int;

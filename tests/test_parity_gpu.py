@@ -254,6 +254,42 @@ def test_render_to_host_and_accumulate(case_table):
         assert np.array_equal(_bits(e.readback_accum()), _bits(singles[0]))
 
 
+def test_render_to_host_async_double_buffer(case_table):
+    """rtce_render_to_host_async: when call k returns, the frames of call k - 1 are in ITS buffer (two page-locked buffers,
+    different poses per call); rtce_sync completes the last call; other tracers and the synchronous form may follow."""
+    case = case_table["default_800x600"]
+    calls = 6
+    with _engine(case, slots=4) as e:
+        w, h, _ = e.level_info(-1, 0)
+        batches, expect = [], []
+        for c in range(calls):
+            rots = np.stack([camera.rotation(0.05 * c + 0.01 * k, 0.02 * k) for k in range(5)])
+            poss = np.array([[0.1 * c, 0.05 * k, 0.0] for k in range(5)], dtype=np.float32)
+            pcs = rt.make_push_constants(rots, poss)
+            batches.append(pcs)
+            expect.append(e.render_to_host(pcs).copy())          # the synchronous form is the reference here
+        pins = [rt.PinnedBuffer((5, h, w)), rt.PinnedBuffer((5, h, w))]
+        for p in pins:
+            p.array[:] = np.nan
+        for c in range(calls):
+            e.render_to_host_async(batches[c], pins[c & 1].array)
+            if c > 0:   # the previous call's buffer is complete now, while this call is still in flight
+                assert np.array_equal(_bits(pins[(c - 1) & 1].array), _bits(expect[c - 1])), c
+        e.sync()
+        assert np.array_equal(_bits(pins[(calls - 1) & 1].array), _bits(expect[calls - 1]))
+        # a tracer that writes window 0 right behind an asynchronous call must wait for its copies
+        e.render_to_host_async(batches[0], pins[0].array)
+        e.trace(batches[3][:4])
+        got = [e.readback(-1, k) for k in range(4)]
+        e.sync()
+        assert np.array_equal(_bits(pins[0].array), _bits(expect[0]))
+        for k in range(4):
+            assert np.array_equal(_bits(got[k]), _bits(expect[3][k])), k
+        assert np.array_equal(_bits(e.render_to_host(batches[1])), _bits(expect[1]))
+        for p in pins:
+            p.free()
+
+
 @pytest.mark.parametrize("groups", [1, 2, 4, 8])
 def test_graph_replay_equals_issued_launches(groups, case_table):
     """RTCE_OPT_GRAPH: a captured launch chain replayed with NEW cameras (they travel through device memory),
@@ -660,6 +696,22 @@ def test_render_rgba8_to_host_matches_shade_readback(shade_case_table):
             e.trace(pcs[k:k + 1])
             e.shade(pcs[k:k + 1])
             assert np.array_equal(out[k], e.readback_color_rgba8(0)), k
+        # asynchronous form, two page-locked buffers: call k returns with call k - 1 complete; mixes with the depth form
+        pins = [rt.PinnedBuffer((7, H, W)), rt.PinnedBuffer((7, H, W))]
+        bufs = [p.array.view(np.uint8).reshape(7, H, W, 4) for p in pins]
+        depth = e.render_to_host(pcs).copy()
+        dpin = rt.PinnedBuffer(depth.shape)
+        for k in range(5):
+            bufs[k & 1][:] = 0
+            e.render_rgba8_to_host_async(pcs, bufs[k & 1])
+            if k > 0:
+                assert np.array_equal(bufs[(k - 1) & 1], out), k
+        e.render_to_host_async(pcs, dpin.array)          # its return completes the last RGBA8 call
+        assert np.array_equal(bufs[0], out)
+        e.sync()
+        assert np.array_equal(_bits(dpin.array), _bits(depth))
+        for p in pins + [dpin]:
+            p.free()
 
 
 @pytest.mark.parametrize("marcher", [1, 2])
