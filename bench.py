@@ -53,7 +53,7 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c1", choices=sorted(WORKLOADS))
     ap.add_argument("--in-flight", type=int, default=None,
-                    help="RTCE_OPT_FRAMES_IN_FLIGHT (library default 6; accumulating workloads: 8)")
+                    help="RTCE_OPT_FRAMES_IN_FLIGHT (default: the library's, 8)")
     ap.add_argument("--strip-ctas", type=int, default=None, help="RTCE_OPT_STRIP_CTAS_PER_SM")
     ap.add_argument("--large-kernel", type=int, default=None, help="RTCE_OPT_LARGE_KERNEL (objCount > 8): 0 auto, 2 register kernel, 3 event-driven kernel")
     ap.add_argument("--graph", type=int, default=None, help="RTCE_OPT_GRAPH")
@@ -665,7 +665,7 @@ def run_ours(args, wl):
     pcs = rt.make_push_constants(rots, poss)
     steps = args.steps if args.steps is not None else 20
     warmup = max(args.warmup if args.warmup is not None else 5, 3)
-    in_flight = args.in_flight if args.in_flight is not None else (8 if accumulate else 6)
+    in_flight = args.in_flight if args.in_flight is not None else 8   # = the library default (kDefaultInFlight)
     slots = min(frames_rank, args.slots or (32 if accumulate else 16), 32)
 
     with torch.cuda.stream(cx.stream):

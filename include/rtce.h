@@ -103,7 +103,8 @@ typedef enum rtce_option {
                                    forks and joins included) is captured once into a CUDA graph and replayed by later
                                    calls with the same batch shape; the per-call cameras travel through device memory.
                                    0 = issue every launch.  Counters and the debug timelines always issue every launch. */
-    RTCE_OPT_FRAMES_IN_FLIGHT = 9, /* 1..8, default 6.  The reference keeps frames in flight behind its swapchain
+    RTCE_OPT_FRAMES_IN_FLIGHT = 9, /* 1..8, default 8 (measured on BASELINE.json configs[1]: 4 -> 196, 6 -> 214,
+                                   8 -> 220 Grays/s).  The reference keeps frames in flight behind its swapchain
                                    (main.rs:859-884: acquire, submit, fence of the PREVIOUS frame).  With W > 1 successive
                                    rtce_trace_batch calls rotate over W windows of frame slots, each with its own streams:
                                    a call starts after everything enqueued on the context's stream so far, but NOT after

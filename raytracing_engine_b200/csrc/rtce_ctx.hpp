@@ -16,7 +16,7 @@ namespace rtce {
 
 constexpr int kMaxGroups = 8;
 constexpr unsigned kOverflowCap = 1u << 19;   // rays per frame group (38 MB each); beyond it long rays stay in their warp
-constexpr int kDefaultInFlight = 6;           // RTCE_OPT_FRAMES_IN_FLIGHT default
+constexpr int kDefaultInFlight = 8;           // RTCE_OPT_FRAMES_IN_FLIGHT default
 constexpr int kAccumLanes = 4;                // chunks of rtce_trace_accumulate in flight, at least
 
 // A lane is one self-contained launch chain: its own stream (plus one per frame group), its own

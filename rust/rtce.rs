@@ -209,7 +209,7 @@ impl ConeMarcher {
     }
 
     /// Frames in flight (src/main.rs:859-884): `w` batches rotate over `w` windows of frame slots
-    /// (RTCE_OPT_FRAMES_IN_FLIGHT = 9); default 6; 1 = strict stream order.
+    /// (RTCE_OPT_FRAMES_IN_FLIGHT = 9); default 8; 1 = strict stream order.
     pub fn set_frames_in_flight(&mut self, w: u32) -> Result<(), Error> {
         let st = unsafe { rtce_set_option(self.ctx, 9, w as i64) };
         self.check(st)

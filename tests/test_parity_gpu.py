@@ -610,7 +610,7 @@ def test_repeat_device_function_matches_the_reference_text():
 
 
 def test_prepare_then_trace_and_default_frames_in_flight(case_table):
-    """rtce_prepare captures every lane's graphs up front; the default (6 frames in flight) gives the bits of strict order."""
+    """rtce_prepare captures every lane's graphs up front; the default (8 frames in flight) gives the bits of strict order."""
     case = case_table["default_800x600"]
     rots, poss = camera.bench_camera_path(28)
     pcs = rt.make_push_constants(rots, poss)
