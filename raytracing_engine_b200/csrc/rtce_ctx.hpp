@@ -27,7 +27,10 @@ constexpr int kAccumLanes = 4;                // chunks of rtce_trace_accumulate
 // chunks the same way.  Lanes are created EAGERLY (rtce_create / RTCE_OPT_FRAMES_IN_FLIGHT) and the
 // launch graphs of a chunk shape are captured for every lane the first time the shape is seen (or by
 // rtce_prepare): no allocation, stream creation or graph instantiation happens on a later call.
-constexpr int kMaxLanes = 8;
+#ifndef RTCE_MAX_LANES
+#define RTCE_MAX_LANES 8
+#endif
+constexpr int kMaxLanes = RTCE_MAX_LANES;
 constexpr int kCamRing = 8;
 struct ChunkGraph { int frames, slot0, lanes; uint64_t version; cudaGraphExec_t exec; uint64_t launches; };   // lanes: 0 = strict order
 struct Lane {
