@@ -850,7 +850,6 @@ def run_ours(args, wl):
 
     hbm_peak, sm_max, peak_src = measured_peaks()
     fp32_peak, fp32_ms = rt.measure_fp32_issue(local_rank, 4096)
-    fp32_packed, _ = rt.measure_fp32_packed(local_rank, 4096)
     if shade is not None:
         shade["frac_of_fp32_issue_peak"] = shade["achieved_tlaneop_per_s"] * 1e12 / fp32_peak
     nominal = 148 * 128 * sm_max * 1e6
@@ -861,11 +860,8 @@ def run_ours(args, wl):
     if os.path.exists(tp):
         with open(tp) as fh:
             traffic = json.load(fh).get("dram_bytes_per_launch")
-    peak_note = ("measured live: rtce_measure_fp32_issue (non-contracted SCALAR FMUL/FADD, register operands: the kernels' own "
-                 f"instruction form); nominal 148 SM x 128 lanes x {sm_max:.0f} MHz = {nominal / 1e12:.1f}.  peak_packed_f32x2 = the same "
-                 "chains on FADD2 / FMUL2 (rtce_measure_fp32_packed): the FP32 pipe's ceiling for separately rounded arithmetic, twice "
-                 "the scalar issue rate; frac_of_packed_peak divides by it (DESIGN.md 'Packed FP32': built twice into the strip kernel, "
-                 "bit-exact, fewer instructions, not faster — the launch is latency-bound per warp)")
+    peak_note = ("measured live: rtce_measure_fp32_issue (non-contracted FMUL/FADD, register operands); "
+                 f"nominal 148 SM x 128 lanes x {sm_max:.0f} MHz = {nominal / 1e12:.1f}")
     frac_note = ("frac counts EXECUTED work: the algorithmic FP32 operations (SURVEY.md 8d: 57 R + 10 E + (12 + 3 N) S, device counters "
                  "equal to the oracle's) of the rays that are really marched; rays resolved by the far-miss shortcut (RTCE_OPT_FAR_MISS: "
                  "parent texel beyond every sphere by more than RENDER_DIST, exactly start + RENDER_DIST) are NOT credited. "
@@ -881,7 +877,6 @@ def run_ours(args, wl):
         bytes_launch = 5 * cnt_launch["R"]
         roofline = {"bound": "fp32_issue", "achieved": executed / t / 1e12, "peak": fp32_peak / 1e12, "unit": "Tlane-op/s",
                     "frac": executed / t / fp32_peak, "traffic": traffic, "peak_source": peak_note,
-                    "peak_packed_f32x2": fp32_packed / 1e12, "frac_of_packed_peak": executed / t / fp32_packed,
                     "frac_reference_algorithm": ops_launch / t / fp32_peak, "far_miss_rays_per_launch": far_launch,
                     "frac_note": frac_note, "frac_of_nominal": executed / t / nominal,
                     "ops_executed_per_launch": executed, "ops_reference_algorithm_per_launch": ops_launch,
@@ -891,8 +886,7 @@ def run_ours(args, wl):
                     "dominant_kernel": dom, "step": step_roof}
     else:
         roofline = dict(step_roof)
-        roofline.update({"bound": "fp32_issue", "peak": fp32_peak * n_gpus / 1e12, "peak_packed_f32x2": fp32_packed * n_gpus / 1e12,
-                         "frac_of_packed_peak": roofline["frac"] * fp32_peak / fp32_packed, "unit": "Tlane-op/s", "traffic": None,
+        roofline.update({"bound": "fp32_issue", "peak": fp32_peak * n_gpus / 1e12, "unit": "Tlane-op/s", "traffic": None,
                          "peak_source": peak_note, "frac_note": frac_note, "step": step_roof,
                          "scope": "all launches of the step, gaps included (no single dominant launch was timed)"})
 

@@ -286,10 +286,6 @@ int rtce_gather_last_ms(rtce_ctx* ctx, float* ms);
  * non-contracted FMUL/FADD chains, timed with CUDA events.  Writes lane-operations per second
  * (the denominator of the FP32-issue roofline) and the kernel time in ms. */
 int rtce_measure_fp32_issue(int device, int iters, double* lane_ops_per_s, double* ms);
-/* The same chains on packed pairs (add / mul .rn.f32x2 = FADD2 / FMUL2 of sm_100a: two separately rounded binary32 operations
- * per lane and instruction, the bits of two scalar instructions).  The FP32 pipe runs them at twice the scalar rate:
- * this, not the scalar issue rate, is the ceiling of separately rounded FP32 arithmetic on the device. */
-int rtce_measure_fp32_packed(int device, int iters, double* lane_ops_per_s, double* ms);
 /* Exhaustive check (all 2^32 float bit patterns, on the GPU) that the short sqrt / reciprocal
  * sequences of the hot kernels return the bits of IEEE sqrt.rn / rcp.rn on their stated domains.
  * out4 = {sqrt mismatches, rcp mismatches, sqrt inputs checked, rcp inputs checked}. */

@@ -28,53 +28,9 @@ __global__ void __launch_bounds__(256) k_fp32_issue(float* sink, int iters, floa
     if (s == 12345.678f) sink[0] = s;   // keep the chains alive
 }
 
-// The same chains on packed pairs: mul.rn.f32x2 / add.rn.f32x2 (SASS FMUL2 / FADD2), two separately rounded binary32
-// operations per lane and instruction.  ptxas contracts mul.rn.f32x2 followed by add.rn.f32x2 into FFMA2 in spite of the
-// .rn modifiers and --fmad=false (DESIGN.md "Packed FP32"), so the sum is written fma(v, ONE, b) with ONE = (1, 1) from a
-// kernel argument the optimiser cannot see through: one rounding of v + b, and nothing can be fused into it.
-__global__ void __launch_bounds__(256) k_fp32_packed(float* sink, int iters, float a, float b, float one) {
-    unsigned long long v[kChains / 2], A, B, ONE;
-    asm("mov.b64 %0, {%1, %1};" : "=l"(ONE) : "f"(one));
-    asm("mov.b64 %0, {%1, %1};" : "=l"(A) : "f"(a));
-    asm("mov.b64 %0, {%1, %1};" : "=l"(B) : "f"(b));
-#pragma unroll
-    for (int i = 0; i < kChains / 2; i++) {
-        const float lo = (float)(threadIdx.x + 2 * i) * 1e-3f, hi = (float)(threadIdx.x + 2 * i + 1) * 1e-3f;
-        asm("mov.b64 %0, {%1, %2};" : "=l"(v[i]) : "f"(lo), "f"(hi));
-    }
-    for (int it = 0; it < iters; it++) {
-#pragma unroll 4
-        for (int u = 0; u < 4; u++) {
-#pragma unroll
-            for (int i = 0; i < kChains / 2; i++) {
-                asm volatile("mul.rn.f32x2 %0, %0, %1;" : "+l"(v[i]) : "l"(A));
-                asm volatile("fma.rn.f32x2 %0, %0, %1, %2;" : "+l"(v[i]) : "l"(ONE), "l"(B));
-            }
-        }
-    }
-    float s = 0.0f;
-#pragma unroll
-    for (int i = 0; i < kChains / 2; i++) {
-        float lo, hi;
-        asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v[i]));
-        s += lo + hi;
-    }
-    if (s == 12345.678f) sink[0] = s;   // keep the chains alive
-}
-
 }  // namespace
 
-static int measure_issue(int device, int iters, bool packed, double* lane_ops_per_s, double* ms_out);
-
 extern "C" int rtce_measure_fp32_issue(int device, int iters, double* lane_ops_per_s, double* ms_out) {
-    return measure_issue(device, iters, false, lane_ops_per_s, ms_out);
-}
-
-extern "C" int rtce_measure_fp32_packed(int device, int iters, double* lane_ops_per_s, double* ms_out) {
-    return measure_issue(device, iters, true, lane_ops_per_s, ms_out);
-}
-
-static int measure_issue(int device, int iters, bool packed, double* lane_ops_per_s, double* ms_out) {
     if (!lane_ops_per_s || iters < 1) return RTCE_ERR_INVALID;
     int prev = 0, sms = 0;
     if (cudaGetDevice(&prev) != cudaSuccess) return RTCE_ERR_CUDA;
@@ -87,13 +43,11 @@ static int measure_issue(int device, int iters, bool packed, double* lane_ops_pe
     cudaEventCreate(&e0);
     cudaEventCreate(&e1);
     const int blocks = sms * 8, threads = 256;   // 2048 threads / SM: full occupancy
-    if (packed) k_fp32_packed<<<blocks, threads>>>(sink, 64, 0.999f, 1e-3f, 1.0f);   // warm-up
-    else k_fp32_issue<<<blocks, threads>>>(sink, 64, 0.999f, 1e-3f);
+    k_fp32_issue<<<blocks, threads>>>(sink, 64, 0.999f, 1e-3f);   // warm-up
     float best = 1e30f;
     for (int rep = 0; rep < 5; rep++) {
         cudaEventRecord(e0);
-        if (packed) k_fp32_packed<<<blocks, threads>>>(sink, iters, 0.999f, 1e-3f, 1.0f);
-        else k_fp32_issue<<<blocks, threads>>>(sink, iters, 0.999f, 1e-3f);
+        k_fp32_issue<<<blocks, threads>>>(sink, iters, 0.999f, 1e-3f);
         cudaEventRecord(e1);
         if (cudaEventSynchronize(e1) != cudaSuccess) { rc = RTCE_ERR_CUDA; break; }
         float ms = 0.0f;

@@ -35,7 +35,7 @@ PUSH_CONSTANTS_DTYPE = np.dtype(
 assert PUSH_CONSTANTS_DTYPE.itemsize == 40
 
 EXPORTS = [
-    "rtce_trace_noalloc", "rtce_measure_fp32_packed", "rtce_abi_version", "rtce_create", "rtce_destroy", "rtce_last_error", "rtce_status_string",
+    "rtce_trace_noalloc", "rtce_abi_version", "rtce_create", "rtce_destroy", "rtce_last_error", "rtce_status_string",
     "rtce_set_option", "rtce_set_stream", "rtce_set_scene", "rtce_set_spheres", "rtce_set_view",
     "rtce_set_rect", "rtce_level_count", "rtce_level_info", "rtce_host_level_count",
     "rtce_host_level_dims", "rtce_host_image_size", "rtce_trace", "rtce_trace_batch",
@@ -126,7 +126,6 @@ def load_library() -> C.CDLL:
         "rtce_readback_color_rgba8": (i32, [vp, i32, vp]),
         "rtce_get_shade_counters": (i32, [vp, C.POINTER(C.c_uint64)]),
         "rtce_measure_fp32_issue": (i32, [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
-        "rtce_measure_fp32_packed": (i32, [i32, i32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
         "rtce_selftest_math": (i32, [i32, C.POINTER(C.c_uint64)]),
         "rtce_debug_strip_timeline": (i32, [vp, i32, vp, i32]),
         "rtce_debug_launch_timeline": (i32, [vp, vp, i32]),
@@ -173,15 +172,6 @@ def measure_fp32_issue(device: int = 0, iters: int = 4096):
     r = load_library().rtce_measure_fp32_issue(int(device), int(iters), C.byref(ops), C.byref(ms))
     if r != RTCE_OK:
         raise RtceError(f"rtce_measure_fp32_issue: {r}")
-    return ops.value, ms.value
-
-
-def measure_fp32_packed(device: int = 0, iters: int = 4096):
-    """The same on packed pairs (FADD2 / FMUL2): the device's ceiling for separately rounded FP32 arithmetic."""
-    ops, ms = C.c_double(), C.c_double()
-    r = load_library().rtce_measure_fp32_packed(int(device), int(iters), C.byref(ops), C.byref(ms))
-    if r != RTCE_OK:
-        raise RtceError(f"rtce_measure_fp32_packed: {r}")
     return ops.value, ms.value
 
 

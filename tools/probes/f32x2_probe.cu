@@ -1,7 +1,10 @@
-// Do the packed FP32 instructions of sm_100a (add / mul .rn.f32x2 -> FADD2 / FMUL2: two separately rounded binary32
-// operations per lane, the same bits as two scalar instructions) raise the FP32 rate, or only halve the issue slots?
-// Per thread 16 independent accumulators, alternating add and mul (never contracted), scalar against packed, alone and
-// with 16 independent integer instructions per iteration beside them (an "issue-bound" mix like the strip kernel's).
+// A probe that was FOOLED, kept as the demonstration of a ptxas hazard.  It was meant to compare scalar add / mul chains
+// with the same chains on packed pairs (add / mul .rn.f32x2 -> FADD2 / FMUL2) and printed 36.7 against 69.5 Tlane-op/s.
+// The SASS of its packed loop holds 400 FFMA2 and only 64 FADD2 / FMUL2: ptxas contracted mul.rn.f32x2 followed (one
+// iteration later) by add.rn.f32x2 into FFMA2 — explicit .rn modifiers, `asm volatile` and --fmad=false notwithstanding —
+// so the "doubled rate" is the ordinary FMA rate counted as two operations, and the bits are not those of the separately
+// rounded operations.  The honest measurement is f32x2_rates.cu: FADD2, FMUL2 and FFMA2 each issue at 0.5 per clock and
+// scheduler, i.e. the SAME results per second as the scalar instructions, in half the issue slots.
 // build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 --fmad=false -o variants/f32x2_probe tools/probes/f32x2_probe.cu
 #include <cstdio>
 #include <cuda_runtime.h>
